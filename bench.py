@@ -1,0 +1,268 @@
+#!/usr/bin/env python
+"""Headline benchmark: 512^3 wave solve, K time steps, on N B200s of one node.
+
+Metric (BASELINE.json): wall time (s) and GLUP/s at 512^3 K=20, device-timed, max
+over ranks.  The reference's published numbers are 0.752 s / 3.55 GLUP/s on one
+P100 and 0.505 s / 5.28 GLUP/s on two (readme.md:99-100; report.pdf p.16 §4.4).
+
+A bench "step" is one time step of the scheme (one fused kernel launch per GPU:
+stencil + in-kernel P2P halo exchange + error epilogue).  ``--steps K`` runs the
+reference's workload exactly when K = 20: Taylor step + 19 leapfrog steps, error
+norms on every 2nd step like the reference prints them.  Timed region: K steps,
+CUDA events, barrier + synchronize on both sides, max over ranks; repeated
+``--reps`` times (each repetition re-initialises the field outside the timed
+region) and the median repetition is reported.  The two 1.16 GB field arrays are
+far larger than the 126 MB L2, so no flush is needed between iterations.
+
+``--impl reference``: the reference tree ships no source (only readme.md and
+report.pdf), so it cannot be installed; prints the "unavailable" line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+PUBLISHED_GLUPS = {1: 3.55, 2: 5.28}      # BASELINE.md §1 (derived from 0.752 s / 0.505 s)
+PUBLISHED_WALL_S = {1: 0.752, 2: 0.505}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU while the timed region runs."""
+
+    def __init__(self, index: int, period: float = 0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksThrottleReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def stop(self) -> dict:
+        self._stop_evt.set()
+        if self.is_alive():
+            self.join(timeout=1.0)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def reference_arm() -> int:
+    print(json.dumps({
+        "impl": "reference",
+        "unavailable": "reference tree has no source code or build (readme.md + report.pdf only): "
+                       "pip reports 'neither setup.py nor pyproject.toml found'; published numbers in BASELINE.md stand"}))
+    return 0
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
+    ap.add_argument("--N", type=int, default=512)
+    ap.add_argument("--L", type=float, default=1.0)
+    ap.add_argument("--tau", type=float, default=1e-3)
+    ap.add_argument("--bc", default="ddd")
+    ap.add_argument("--backend", default="fused", choices=("fused", "nccl"))
+    ap.add_argument("--decomp", default="block")
+    ap.add_argument("--variant", type=int, default=-1)
+    ap.add_argument("--zchunk", type=int, default=0)
+    ap.add_argument("--reps", type=int, default=7)
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--every", type=int, default=2)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm()
+
+    import torch
+    import torch.distributed as dist
+    from mpi_cuda_b200 import WaveProblem
+    from mpi_cuda_b200.models.analytic import oracle_errors
+    from mpi_cuda_b200.parallel.decomp import parse_dims
+    from mpi_cuda_b200.parallel.launch import init_distributed
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device: bench.py needs a B200 (run under gpurun)"}))
+        return 1
+    rank, world, device = init_distributed("nccl")
+    if world != args.gpus:
+        if rank == 0:
+            print(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}; using {world}", file=sys.stderr)
+    K, W = args.steps, max(args.warmup, 3)
+    p = WaveProblem(args.N, args.L, args.tau, K, bc=args.bc)
+    p.check_cfl()
+    dims = parse_dims(args.decomp, world)
+
+    def barrier():
+        torch.cuda.synchronize(device)
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(x: float) -> float:
+        t = torch.tensor([x], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    sampler = ClockSampler(device.index or 0)
+    extra = {}
+    if args.backend == "fused":
+        from mpi_cuda_b200.parallel.fused import FusedSolver, StreamingSession
+        s = FusedSolver(p, dims, device, every=args.every, variant=args.variant, zchunk=args.zchunk,
+                        use_graph=not args.no_graph)
+        # ---- warm-up: W untimed steps (also loads the module, maps peers) ----
+        s.init()
+        s._enqueue_steps(1, min(W, K))
+        barrier()
+        if s.use_graph:
+            s.capture()
+        times = []
+        launches0 = s.kernel_launches
+        sampler.start()
+        for _ in range(args.reps):
+            s.init()                       # untimed: layer 0, flags reset, barrier
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            e0.record()
+            s.run_steps()                  # EXACTLY K steps
+            e1.record()
+            barrier()
+            times.append(max_over_ranks(e0.elapsed_time(e1)))
+        clocks = sampler.stop()
+        launches = (s.kernel_launches - launches0) // args.reps
+        s.check_status()
+        trace = s.gather_trace()
+        extra["plan"] = s.describe()
+        # ---- end to end through the public step API: per step H2D of the step's
+        #      input (time factor, pinned host) and D2H of the step's result ----
+        e2e = None
+        if not args.no_e2e:
+            sess = StreamingSession(s)
+            e2e_times = []
+            for _ in range(max(3, args.reps // 2)):
+                barrier()
+                t0 = time.perf_counter()
+                sess.start()               # tables H2D from pinned memory + init kernel + barrier
+                for n in range(1, K + 1):
+                    sess.step(n)
+                barrier()
+                e2e_times.append(max_over_ranks(time.perf_counter() - t0))
+            sess.close()
+            t_e2e = statistics.median(e2e_times)
+            e2e = {"value": p.updates / t_e2e / 1e9, "unit": "GLUP/s", "wall_s": t_e2e,
+                   "h2d_bytes_per_step": sess.H2D_BYTES_PER_STEP + sess.table_bytes / K,
+                   "d2h_bytes_per_step": sess.D2H_BYTES_PER_STEP,
+                   "includes": "analytic tables H2D (pinned) + layer-0 init + K x (8 B H2D, fused step, 16 B D2H + sync)"}
+    else:
+        from mpi_cuda_b200.parallel.exchange import CudaBlockOps, ExchangeSolver
+        s = ExchangeSolver(p, dims, lambda pp, b: CudaBlockOps(pp, b, device, args.variant, args.zchunk),
+                           every=args.every, backend_name="nccl")
+        s.run(time_phases=False)
+        times = []
+        sampler.start()
+        l0 = s.ops.plan.launches
+        for _ in range(args.reps):
+            r = s.run(time_phases=False)
+            times.append(r.phases["loop"] * 1e3)
+        clocks = sampler.stop()
+        launches = (s.ops.plan.launches - l0) // args.reps
+        trace = r.trace
+        e2e = None
+
+    t_ms = statistics.median(times)
+    glups = p.updates / (t_ms / 1e3) / 1e9
+    # correctness guard: the error at the last reporting step must match the closed form
+    valid = None
+    if trace:
+        n, _, mx, l2 = trace[-1]
+        omx, ol2 = oracle_errors(p, n)
+        valid = bool(abs(mx - omx) <= 1e-13 + 1e-5 * omx and abs(l2 - ol2) <= 1e-13 + 1e-5 * ol2)
+    pub = PUBLISHED_GLUPS.get(world, PUBLISHED_GLUPS[2])
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            peaks = json.load(fh)
+    except Exception:
+        pass
+    hbm = peaks.get("hbm_gbs", 6650.0)
+    from mpi_cuda_b200.parallel.decomp import plan_all
+    blocks = plan_all(p, dims)
+    bytes_per_gpu = max((b.n[0] + 2) * (b.n[1] + 2) * (b.n[2] + 2) for b in blocks) * 24
+    halo_bytes = max(b.halo_bytes_per_step() for b in blocks)
+    t_roof_ms = max(bytes_per_gpu / (hbm * 1e9), halo_bytes / 770e9) * 1e3
+    out = {
+        "metric": "GLUP/s at %d^3 grid, K=%d steps, fp64, device-timed max over ranks (wall_s = total)" % (args.N, K),
+        "value": glups, "unit": "GLUP/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": t_ms / K, "wall_s": t_ms / 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": glups / pub, "dtype": "fp64", "data": "synthetic (analytic-solution initial layers)",
+        "config": {"model": "wave3d leapfrog 7-point", "grid": f"{args.N}^3", "global_batch": p.n_unknowns,
+                   "seq_len": K, "parallelism": f"spatial {dims[0]}x{dims[1]}x{dims[2]}", "backend": args.backend,
+                   "bc": args.bc, "L": args.L, "tau": args.tau, "report_every": args.every,
+                   "l2_policy": "inputs larger than L2 (2 x %.2f GB fields per GPU vs 126 MB L2), no flush"
+                                % (bytes_per_gpu / 24 * 8 / 1e9),
+                   "reps": args.reps, "rep_ms": [round(t, 4) for t in times], "cuda_graph": not args.no_graph,
+                   "published_baseline": {"glups": pub, "wall_s": PUBLISHED_WALL_S.get(world, 0.505),
+                                          "hardware": "%d x P100" % min(world, 2)}},
+        "roofline": {"hbm_gbs_measured": hbm, "bytes_per_gpu_per_step": bytes_per_gpu,
+                     "halo_bytes_per_gpu_per_step": halo_bytes, "roofline_ms_per_step": t_roof_ms,
+                     "fraction_of_roofline": t_roof_ms / (t_ms / K), "of": "measured" if peaks else "fallback"},
+        "clocks": clocks, "gpu_launches": launches, "validated_vs_oracle": valid,
+        "last_error_line": trace[-1] if trace else None,
+    }
+    if e2e is not None:
+        out["e2e"] = e2e
+    out.update(extra)
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1 and dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

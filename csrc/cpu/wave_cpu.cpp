@@ -1,0 +1,485 @@
+// wave_cpu.cpp — native CPU solvers: sequential, OpenMP, and rank-threaded
+// ("MPI-like") block-decomposed versions of the explicit 3-D wave scheme.
+//
+// Native equivalents of the reference programs wave.cpp, openmpwave.cpp, mpi.cpp
+// and mpiomp.cpp, which are named in readme.md:34-48 and described in
+// report.pdf p.20-26 §5 but are not shipped as files.  Written from the published
+// scheme (report.pdf p.5 §2) only.
+//
+// The distributed version keeps the reference's structure — block decomposition,
+// per-step halo exchange as a separately timed phase, boundary processing as a
+// separately timed phase, global max / sum reductions for the error (report.pdf
+// p.16 §4.4 second table) — but there is no MPI on the target image, so ranks are
+// threads of one process and MPI_Sendrecv is a small mailbox (`Mailbox` below)
+// with the same pack -> sendrecv -> unpack shape.
+#include "wave3d_cpu.h"
+#include "stencil_core.h"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <condition_variable>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <thread>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+namespace {
+
+using clk = std::chrono::steady_clock;
+inline double now_s() {
+  return std::chrono::duration<double>(clk::now().time_since_epoch()).count();
+}
+
+inline int64_t plane_stride(const W3dBlock* b) { return (int64_t)(b->n[1] + 2) * b->pitch; }
+inline int64_t idx(const W3dBlock* b, int i, int j, int k) {
+  return ((int64_t)k * (b->n[1] + 2) + j) * b->pitch + b->xoff + i;
+}
+
+// split `n` items over `parts`, remainder to the first blocks (same rule as the
+// Python planner in parallel/decomp.py)
+inline void split(int n, int parts, int r, int* lo, int* cnt) {
+  int q = n / parts, rem = n % parts;
+  *cnt = q + (r < rem ? 1 : 0);
+  *lo = r * q + std::min(r, rem);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* w3d_cpu_version(void) { return "wave3d-cpu 1.0"; }
+
+int w3d_cpu_max_threads(void) {
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
+
+int64_t w3d_block_elems(const W3dBlock* b) {
+  return (int64_t)(b->n[2] + 2) * (b->n[1] + 2) * b->pitch;
+}
+
+void w3d_cpu_init(double* u, const W3dBlock* b, const double* sx, const double* sy,
+                  const double* sz, int threads) {
+  const int nx = b->n[0], ny = b->n[1], nz = b->n[2];
+  (void)threads;
+#pragma omp parallel for collapse(2) num_threads(threads) schedule(static)
+  for (int k = 0; k < nz + 2; ++k)
+    for (int j = 0; j < ny + 2; ++j) {
+      double* row = u + idx(b, 0, j, k);
+      const double syz = sy[j] * sz[k];
+      for (int i = 0; i < nx + 2; ++i) row[i] = sx[i] * syz;
+    }
+}
+
+void w3d_cpu_step(double* pn, const double* cur, const W3dBlock* b, double a, double bb,
+                  const double c[3], const int32_t lo[3], const int32_t hi[3], int threads) {
+  const int64_t sy = b->pitch, sz = plane_stride(b);
+  const double cx = c[0], cy = c[1], cz = c[2];
+  (void)threads;
+#pragma omp parallel for collapse(2) num_threads(threads) schedule(static)
+  for (int k = lo[2]; k < hi[2]; ++k)
+    for (int j = lo[1]; j < hi[1]; ++j) {
+      const double* cr = cur + idx(b, 0, j, k);
+      double* pr = pn + idx(b, 0, j, k);
+#pragma omp simd
+      for (int i = lo[0]; i < hi[0]; ++i) {
+        pr[i] = w3d_node(cr[i], pr[i], cr[i - 1], cr[i + 1], cr[i - sy], cr[i + sy], cr[i - sz],
+                         cr[i + sz], a, bb, cx, cy, cz);
+      }
+    }
+}
+
+void w3d_cpu_error(const double* u, const W3dBlock* b, const double* sx, const double* sy,
+                   const double* sz, double ct, double* max_err, double* sum_sq, int threads) {
+  const int nx = b->n[0], ny = b->n[1], nz = b->n[2];
+  double mx = 0.0, s2 = 0.0;
+  (void)threads;
+  // per-plane partial sums added in plane order -> result independent of thread count
+  std::vector<double> pm(nz + 2, 0.0), ps(nz + 2, 0.0);
+#pragma omp parallel for num_threads(threads) schedule(static)
+  for (int k = 1; k <= nz; ++k) {
+    const double szt = sz[k] * ct;
+    double m = 0.0, s = 0.0;
+    for (int j = 1; j <= ny; ++j) {
+      const double* row = u + idx(b, 0, j, k);
+      const double syj = sy[j];
+      double rs = 0.0;
+      for (int i = 1; i <= nx; ++i) {
+        double e = w3d_abs_err(row[i], sx[i] * syj, szt);
+        m = e > m ? e : m;
+        rs = fma(e, e, rs);
+      }
+      s += rs;
+    }
+    pm[k] = m;
+    ps[k] = s;
+  }
+  for (int k = 1; k <= nz; ++k) {
+    mx = std::max(mx, pm[k]);
+    s2 += ps[k];
+  }
+  *max_err = mx;
+  *sum_sq = s2;
+}
+
+void w3d_cpu_wrap(double* u, const W3dBlock* b, int axis) {
+  const int nx = b->n[0], ny = b->n[1], nz = b->n[2];
+  if (axis == 0) {
+    for (int k = 0; k < nz + 2; ++k)
+      for (int j = 0; j < ny + 2; ++j) {
+        double* row = u + idx(b, 0, j, k);
+        row[0] = row[nx];
+        row[nx + 1] = row[1];
+      }
+  } else if (axis == 1) {
+    for (int k = 0; k < nz + 2; ++k) {
+      std::memcpy(u + idx(b, 0, 0, k), u + idx(b, 0, ny, k), sizeof(double) * (nx + 2));
+      std::memcpy(u + idx(b, 0, ny + 1, k), u + idx(b, 0, 1, k), sizeof(double) * (nx + 2));
+    }
+  } else {
+    for (int j = 0; j < ny + 2; ++j) {
+      std::memcpy(u + idx(b, 0, j, 0), u + idx(b, 0, j, nz), sizeof(double) * (nx + 2));
+      std::memcpy(u + idx(b, 0, j, nz + 1), u + idx(b, 0, j, 1), sizeof(double) * (nx + 2));
+    }
+  }
+}
+
+int64_t w3d_cpu_face_elems(const W3dBlock* b, int axis) {
+  const int a = (axis + 1) % 3, c = (axis + 2) % 3;
+  return (int64_t)b->n[a] * b->n[c];
+}
+
+static inline void face_iter(const W3dBlock* b, int axis, int side, int ghost, int* fixed) {
+  const int n = b->n[axis];
+  *fixed = side == 0 ? (ghost ? 0 : 1) : (ghost ? n + 1 : n);
+}
+
+void w3d_cpu_pack(const double* u, const W3dBlock* b, int axis, int side, int ghost, double* buf) {
+  int f;
+  face_iter(b, axis, side, ghost, &f);
+  const int nx = b->n[0], ny = b->n[1], nz = b->n[2];
+  int64_t q = 0;
+  if (axis == 0) {
+    for (int k = 1; k <= nz; ++k)
+      for (int j = 1; j <= ny; ++j) buf[q++] = u[idx(b, f, j, k)];
+  } else if (axis == 1) {
+    for (int k = 1; k <= nz; ++k) {
+      std::memcpy(buf + q, u + idx(b, 1, f, k), sizeof(double) * nx);
+      q += nx;
+    }
+  } else {
+    for (int j = 1; j <= ny; ++j) {
+      std::memcpy(buf + q, u + idx(b, 1, j, f), sizeof(double) * nx);
+      q += nx;
+    }
+  }
+}
+
+void w3d_cpu_unpack(double* u, const W3dBlock* b, int axis, int side, int ghost, const double* buf) {
+  int f;
+  face_iter(b, axis, side, ghost, &f);
+  const int nx = b->n[0], ny = b->n[1], nz = b->n[2];
+  int64_t q = 0;
+  if (axis == 0) {
+    for (int k = 1; k <= nz; ++k)
+      for (int j = 1; j <= ny; ++j) u[idx(b, f, j, k)] = buf[q++];
+  } else if (axis == 1) {
+    for (int k = 1; k <= nz; ++k) {
+      std::memcpy(u + idx(b, 1, f, k), buf + q, sizeof(double) * nx);
+      q += nx;
+    }
+  } else {
+    for (int j = 1; j <= ny; ++j) {
+      std::memcpy(u + idx(b, 1, j, f), buf + q, sizeof(double) * nx);
+      q += nx;
+    }
+  }
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Rank-threaded distributed driver
+// ---------------------------------------------------------------------------
+namespace {
+
+// A blocking point-to-point channel with MPI_Sendrecv-like semantics between
+// ranks that are threads of this process.
+class Mailbox {
+ public:
+  explicit Mailbox(int nranks) : n_(nranks), slots_((size_t)nranks * nranks * 6) {}
+  // tag in [0,6): axis*2+side of the *receiver's* ghost face
+  void send(int src, int dst, int tag, const double* buf, int64_t count) {
+    Slot& s = slot(src, dst, tag);
+    std::unique_lock<std::mutex> lk(s.m);
+    s.cv.wait(lk, [&] { return !s.full; });
+    s.data.assign(buf, buf + count);
+    s.full = true;
+    s.cv.notify_all();
+  }
+  void recv(int src, int dst, int tag, double* buf, int64_t count) {
+    Slot& s = slot(src, dst, tag);
+    std::unique_lock<std::mutex> lk(s.m);
+    s.cv.wait(lk, [&] { return s.full; });
+    std::memcpy(buf, s.data.data(), sizeof(double) * count);
+    s.full = false;
+    s.cv.notify_all();
+  }
+
+ private:
+  struct Slot {
+    std::mutex m;
+    std::condition_variable cv;
+    std::vector<double> data;
+    bool full = false;
+  };
+  Slot& slot(int src, int dst, int tag) { return slots_[((size_t)src * n_ + dst) * 6 + tag]; }
+  int n_;
+  std::vector<Slot> slots_;
+};
+
+class Barrier {
+ public:
+  explicit Barrier(int n) : n_(n) {}
+  void wait() {
+    std::unique_lock<std::mutex> lk(m_);
+    int gen = gen_;
+    if (++count_ == n_) {
+      count_ = 0;
+      ++gen_;
+      cv_.notify_all();
+    } else {
+      cv_.wait(lk, [&] { return gen != gen_; });
+    }
+  }
+
+ private:
+  std::mutex m_;
+  std::condition_variable cv_;
+  int n_, count_ = 0, gen_ = 0;
+};
+
+struct Shared {
+  const W3dCpuRun* run;
+  int nranks;
+  Mailbox* mail;
+  Barrier* bar;
+  std::vector<double> red_max, red_sum;             // per-rank contributions
+  std::vector<std::vector<double>> phases;          // per-rank 5 phases
+  double* trace;
+};
+
+struct RankCtx {
+  int rank, coord[3], nbr[3][2];   // neighbour rank or -1
+  int lo[3], n[3];                 // first global unknown index, local unknowns
+};
+
+void make_tables(const W3dCpuRun* r, const RankCtx& c, std::vector<double> tab[3]) {
+  for (int d = 0; d < 3; ++d) {
+    const int N = r->N[d];
+    const int m = r->periodic[d] ? 2 : 1;
+    tab[d].resize(c.n[d] + 2);
+    for (int l = 0; l < c.n[d] + 2; ++l) {
+      long g = (long)c.lo[d] - 1 + l;          // global node index of local index l
+      g = ((g % N) + N) % N;                   // periodic wrap (no-op for Dirichlet range)
+      if (!r->periodic[d] && ((long)c.lo[d] - 1 + l) == N) g = N;
+      double v = std::sin(m * M_PI * (double)g / (double)N);
+      if (g == 0 || g == N || (m == 2 && 2 * g == N)) v = 0.0;
+      tab[d][l] = v;
+    }
+  }
+}
+
+void rank_main(Shared* sh, int rank) {
+  const W3dCpuRun* r = sh->run;
+  RankCtx c;
+  c.rank = rank;
+  // rank -> coords, x fastest (same as parallel/decomp.py)
+  c.coord[0] = rank % r->dims[0];
+  c.coord[1] = (rank / r->dims[0]) % r->dims[1];
+  c.coord[2] = rank / (r->dims[0] * r->dims[1]);
+  auto rank_of = [&](int cx, int cy, int cz) { return (cz * r->dims[1] + cy) * r->dims[0] + cx; };
+  for (int d = 0; d < 3; ++d) {
+    const int unknowns = r->periodic[d] ? r->N[d] : r->N[d] - 1;
+    const int first = r->periodic[d] ? 0 : 1;
+    int lo, cnt;
+    split(unknowns, r->dims[d], c.coord[d], &lo, &cnt);
+    c.lo[d] = first + lo;
+    c.n[d] = cnt;
+    for (int s = 0; s < 2; ++s) {
+      int cc[3] = {c.coord[0], c.coord[1], c.coord[2]};
+      cc[d] += s == 0 ? -1 : 1;
+      if (cc[d] < 0 || cc[d] >= r->dims[d]) {
+        if (!r->periodic[d]) { c.nbr[d][s] = -1; continue; }
+        cc[d] = (cc[d] + r->dims[d]) % r->dims[d];
+      }
+      c.nbr[d][s] = rank_of(cc[0], cc[1], cc[2]);
+    }
+  }
+  const int T = std::max(1, r->threads);
+  W3dBlock b;
+  b.n[0] = c.n[0]; b.n[1] = c.n[1]; b.n[2] = c.n[2];
+  b.xoff = 0; b.pitch = c.n[0] + 2;
+  const int64_t elems = w3d_block_elems(&b);
+  double ph[5] = {0, 0, 0, 0, 0};
+  const double t_total0 = now_s();
+
+  // ---- init: u0 analytic everywhere (ghosts too), second array zero ----
+  double t0 = now_s();
+  std::vector<double> tab[3];
+  make_tables(r, c, tab);
+  std::vector<double> A(elems), B(elems, 0.0);
+  w3d_cpu_init(A.data(), &b, tab[0].data(), tab[1].data(), tab[2].data(), T);
+  ph[1] += now_s() - t0;
+
+  double h[3], cf[3], chalf[3], at2 = 0.0;
+  for (int d = 0; d < 3; ++d) {
+    h[d] = r->L[d] / r->N[d];
+    cf[d] = r->tau * r->tau / (h[d] * h[d]);
+    chalf[d] = 0.5 * cf[d];
+    const double m = r->periodic[d] ? 2.0 : 1.0;
+    at2 += (m / r->L[d]) * (m / r->L[d]);
+  }
+  const double a_t = M_PI * std::sqrt(at2);
+
+  std::vector<double> sbuf[3][2], rbuf[3][2];
+  for (int d = 0; d < 3; ++d)
+    for (int s = 0; s < 2; ++s)
+      if (c.nbr[d][s] >= 0) {
+        sbuf[d][s].resize(w3d_cpu_face_elems(&b, d));
+        rbuf[d][s].resize(w3d_cpu_face_elems(&b, d));
+      }
+
+  // interior = unknowns not adjacent to a face that has a neighbour; the shell is
+  // computed in a separate, separately timed pass ("boundary processing").
+  int ilo[3], ihi[3];
+  for (int d = 0; d < 3; ++d) {
+    ilo[d] = 1 + (c.nbr[d][0] >= 0 ? 1 : 0);
+    ihi[d] = c.n[d] + 1 - (c.nbr[d][1] >= 0 ? 1 : 0);
+    if (ihi[d] < ilo[d]) ihi[d] = ilo[d];
+  }
+
+  double* cur = A.data();
+  double* prv = B.data();
+  for (int n = 1; n <= r->K; ++n) {
+    const bool taylor = (n == 1);
+    const double a = taylor ? 1.0 : 2.0, bb = taylor ? 0.0 : -1.0;
+    const double* cc = taylor ? chalf : cf;
+    // ---- interior ----
+    t0 = now_s();
+    w3d_cpu_step(prv, cur, &b, a, bb, cc, ilo, ihi, T);
+    ph[2] += now_s() - t0;
+    // ---- shell slabs (disjoint cover of the complement of the interior) ----
+    t0 = now_s();
+    {
+      // peel z slabs (full xy extent), then y slabs, then x slabs: a disjoint cover
+      int lo[3] = {1, 1, 1}, hi[3] = {c.n[0] + 1, c.n[1] + 1, c.n[2] + 1};
+      for (int d = 2; d >= 0; --d) {
+        int l2[3] = {lo[0], lo[1], lo[2]}, h2[3] = {hi[0], hi[1], hi[2]};
+        if (ilo[d] > lo[d]) {
+          h2[d] = ilo[d];
+          w3d_cpu_step(prv, cur, &b, a, bb, cc, l2, h2, T);
+          h2[d] = hi[d];
+        }
+        if (ihi[d] < hi[d]) {
+          l2[d] = ihi[d];
+          w3d_cpu_step(prv, cur, &b, a, bb, cc, l2, h2, T);
+        }
+        lo[d] = ilo[d];
+        hi[d] = ihi[d];
+      }
+    }
+    ph[3] += now_s() - t0;
+    std::swap(cur, prv);  // cur now holds level n
+    // ---- halo exchange of level n ----
+    t0 = now_s();
+    for (int d = 0; d < 3; ++d) {
+      for (int s = 0; s < 2; ++s) {
+        const int dst = c.nbr[d][s];
+        if (dst < 0) continue;
+        if (dst == rank) continue;  // handled by wrap below
+        w3d_cpu_pack(cur, &b, d, s, 0, sbuf[d][s].data());
+        // my side-s edge becomes the neighbour's opposite ghost
+        sh->mail->send(rank, dst, d * 2 + (1 - s), sbuf[d][s].data(), (int64_t)sbuf[d][s].size());
+      }
+      for (int s = 0; s < 2; ++s) {
+        const int src = c.nbr[d][s];
+        if (src < 0) continue;
+        if (src == rank) continue;
+        sh->mail->recv(src, rank, d * 2 + s, rbuf[d][s].data(), (int64_t)rbuf[d][s].size());
+        w3d_cpu_unpack(cur, &b, d, s, 1, rbuf[d][s].data());
+      }
+      if (c.nbr[d][0] == rank) w3d_cpu_wrap(cur, &b, d);
+    }
+    ph[4] += now_s() - t0;
+    // ---- error + reductions ----
+    if (n % r->every == 0) {
+      double mx, s2;
+      const double ct = std::cos(a_t * r->tau * n);
+      w3d_cpu_error(cur, &b, tab[0].data(), tab[1].data(), tab[2].data(), ct, &mx, &s2, T);
+      sh->red_max[rank] = mx;
+      sh->red_sum[rank] = s2;
+      sh->bar->wait();
+      if (rank == 0) {
+        double gm = 0.0, gs = 0.0;
+        for (int q = 0; q < sh->nranks; ++q) {
+          gm = std::max(gm, sh->red_max[q]);
+          gs += sh->red_sum[q];
+        }
+        double cnt = 1.0;
+        for (int d = 0; d < 3; ++d) cnt *= r->periodic[d] ? r->N[d] : r->N[d] - 1;
+        const double l2 = std::sqrt(gs / cnt);
+        sh->trace[2 * n] = gm;
+        sh->trace[2 * n + 1] = l2;
+        if (r->verbose)
+          std::printf("Step %d, t = %.6f, Max Error = %.6e, L2 Error = %.6e\n", n, n * r->tau, gm, l2);
+      }
+      sh->bar->wait();
+    }
+  }
+  ph[0] = now_s() - t_total0;
+  sh->phases[rank].assign(ph, ph + 5);
+}
+
+}  // namespace
+
+extern "C" int w3d_cpu_solve(const W3dCpuRun* run, double* trace, double* phases) {
+  if (!run || !trace || !phases) return 1;
+  const int nr = run->dims[0] * run->dims[1] * run->dims[2];
+  if (nr < 1) return 2;
+  for (int d = 0; d < 3; ++d) {
+    const int unknowns = run->periodic[d] ? run->N[d] : run->N[d] - 1;
+    if (unknowns / run->dims[d] < 2 && run->dims[d] > 1) return 3;  // blocks need >= 2 unknowns
+    if (unknowns < 1) return 3;
+  }
+  for (int n = 0; n <= run->K; ++n) trace[2 * n] = trace[2 * n + 1] = -1.0;
+  Mailbox mail(nr);
+  Barrier bar(nr);
+  Shared sh;
+  sh.run = run; sh.nranks = nr; sh.mail = &mail; sh.bar = &bar;
+  sh.red_max.assign(nr, 0.0); sh.red_sum.assign(nr, 0.0);
+  sh.phases.resize(nr);
+  sh.trace = trace;
+  if (nr == 1) {
+    rank_main(&sh, 0);
+  } else {
+    std::vector<std::thread> th;
+    for (int q = 0; q < nr; ++q) th.emplace_back(rank_main, &sh, q);
+    for (auto& t : th) t.join();
+  }
+  for (int p = 0; p < 5; ++p) {
+    double m = 0.0;
+    for (int q = 0; q < nr; ++q) m = std::max(m, sh.phases[q][p]);
+    phases[p] = m;
+  }
+  return 0;
+}

@@ -1,0 +1,486 @@
+// kernels.cuh — sm_100a device code of the wave solver.
+//
+// What the reference's mpigpu-1.cu must have contained (K1 init,
+// K2 Taylor, K3 leapfrog, K4 boundary, K5 pack/unpack, K6 error) re-designed for
+// B200.  No reference source exists (readme.md:68 names the file only), so none
+// of this is derived from reference code.
+//
+//  * `tma_role`   — z-marching stencil: one producer lane streams (TX+2)x(TY+2)
+//                   planes of u^n and TXxTY planes of u^{n-1} into a shared-memory
+//                   ring with cp.async.bulk.tensor (TMA) + mbarriers; consumer
+//                   warps keep the z-direction in registers, update in place and
+//                   fold max|err| / sum err^2 into the epilogue.
+//  * `shell_role` — nodes adjacent to a neighbour: acquire the neighbours' flags,
+//                   compute, store locally AND into the neighbours' ghost layers
+//                   over NVLink (plain st.global on peer-mapped addresses); the
+//                   last shell CTA releases the flags for the next level.
+//  * `fused_step_kernel` — both roles in ONE launch: low block indices are shell
+//                   CTAs (scheduled first), the rest stream the interior while the
+//                   P2P stores are in flight.
+#pragma once
+#include "ptx.cuh"
+#include "stencil_core.h"
+#include "wave3d.h"
+
+namespace w3d {
+
+constexpr int kMaxBoxes = 6;
+
+struct Geometry {
+  int n[3];
+  int xoff;
+  long long pitch, plane;
+};
+
+struct PeerDev {
+  int active;
+  int ghost_index;
+  double* field;          // peer array that holds the level being produced
+  long long pitch, plane;
+  unsigned long long* flag;
+};
+
+struct BoxTable {
+  int nboxes;
+  int lo[kMaxBoxes][3];
+  int ext[kMaxBoxes][3];
+  long long prefix[kMaxBoxes + 1];
+};
+
+struct TileGeom {
+  int lo[3], hi[3];   // box [lo,hi) in local unknown indices
+  int ntx, nty, zc, nchunks;
+};
+
+struct ErrCtl {
+  double* out;            // 2 doubles or nullptr
+  double* part_max;
+  double* part_sum;
+  unsigned* ticket;
+};
+
+struct alignas(64) StepParams {
+  CUtensorMap map_halo;   // (TX+2)x(TY+2)x1 boxes of the current level
+  CUtensorMap map_core;   // TX x TY x 1 boxes of the previous level (array updated in place)
+  Geometry g;
+  const double* cur;
+  double* nxt;
+  const double* sx;
+  const double* sy;
+  const double* sz;
+  double a, b, cx, cy, cz, ct;
+  const double* ct_ptr;   // if non-null the time factor is read from device memory (host-fed per step)
+  ErrCtl err;
+  // interior
+  TileGeom tile;
+  // shell
+  BoxTable boxes;
+  int n_shell_ctas;
+  int use_flags;
+  PeerDev peer[6];
+  const unsigned long long* flags_in;
+  unsigned* shell_counter;
+  unsigned* status;
+  unsigned long long level;        // level of `cur`
+  unsigned long long timeout_ns;
+};
+
+// ---------------------------------------------------------------------------
+// error reduction: warp shuffle -> CTA -> per-CTA partial -> last CTA folds all
+// partials in index order (deterministic for a given launch geometry).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void warp_reduce(double& mx, double& s2) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+  }
+}
+
+// All threads of the CTA must call this. red_smem: >= 2*32 doubles + 1 int.
+__device__ void publish_error(const ErrCtl& e, double mx, double s2, double* red_smem) {
+  if (e.out == nullptr) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+  int* is_last = reinterpret_cast<int*>(red_smem + 64);
+  warp_reduce(mx, s2);
+  if (lane == 0) {
+    red_smem[warp] = mx;
+    red_smem[32 + warp] = s2;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    mx = lane < nwarps ? red_smem[lane] : 0.0;
+    s2 = lane < nwarps ? red_smem[32 + lane] : 0.0;
+    warp_reduce(mx, s2);
+    if (lane == 0) {
+      e.part_max[blockIdx.x] = mx;
+      e.part_sum[blockIdx.x] = s2;
+      __threadfence();
+      const unsigned t = atomicAdd(e.ticket, 1u);
+      *is_last = (t == gridDim.x - 1);
+    }
+  }
+  __syncthreads();
+  if (*is_last) {
+    __threadfence();
+    double m = 0.0, s = 0.0;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+      m = fmax(m, __ldcg(e.part_max + i));
+      s += __ldcg(e.part_sum + i);
+    }
+    warp_reduce(m, s);
+    __syncthreads();
+    if (lane == 0) {
+      red_smem[warp] = m;
+      red_smem[32 + warp] = s;
+    }
+    __syncthreads();
+    if (warp == 0) {
+      m = lane < nwarps ? red_smem[lane] : 0.0;
+      s = lane < nwarps ? red_smem[32 + lane] : 0.0;
+      warp_reduce(m, s);
+      if (lane == 0) {
+        e.out[0] = m;
+        e.out[1] = s;
+        *e.ticket = 0u;   // ready for the next launch on this slot
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// shell role
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ long long gidx(const Geometry& g, int i, int j, int k) {
+  return (long long)k * g.plane + (long long)j * g.pitch + g.xoff + i;
+}
+
+// first/stride: this thread's first linear node id and the stride between its nodes
+__device__ void shell_compute(const StepParams& P, long long first, long long stride, bool push,
+                              double& mx, double& s2) {
+  const Geometry& g = P.g;
+  const BoxTable& B = P.boxes;
+  const long long total = B.prefix[B.nboxes];
+  const bool want_err = P.err.out != nullptr;
+  const double ct = P.ct_ptr ? __ldg(P.ct_ptr) : P.ct;
+  for (long long id = first; id < total; id += stride) {
+    int b = 0;
+    while (b + 1 < B.nboxes && id >= B.prefix[b + 1]) ++b;
+    long long l = id - B.prefix[b];
+    const int ex = B.ext[b][0], ey = B.ext[b][1];
+    const int i = B.lo[b][0] + (int)(l % ex);
+    l /= ex;
+    const int j = B.lo[b][1] + (int)(l % ey);
+    const int k = B.lo[b][2] + (int)(l / ey);
+    const long long o = gidx(g, i, j, k);
+    const double* c = P.cur + o;
+    const double v = w3d_node(c[0], P.nxt[o], c[-1], c[1], c[-g.pitch], c[g.pitch], c[-g.plane],
+                              c[g.plane], P.a, P.b, P.cx, P.cy, P.cz);
+    P.nxt[o] = v;
+    if (push) {
+      const int co[3] = {i, j, k};
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          const PeerDev& pr = P.peer[d * 2 + s];
+          if (pr.active && co[d] == (s == 0 ? 1 : g.n[d])) {
+            int q[3] = {i, j, k};
+            q[d] = pr.ghost_index;
+            pr.field[(long long)q[2] * pr.plane + (long long)q[1] * pr.pitch + g.xoff + q[0]] = v;
+          }
+        }
+      }
+    }
+    if (want_err) {
+      const double e = w3d_abs_err(v, P.sx[i] * P.sy[j], P.sz[k] * ct);
+      mx = fmax(mx, e);
+      s2 = fma(e, e, s2);
+    }
+  }
+}
+
+__device__ void shell_wait_flags(const StepParams& P) {
+  if (threadIdx.x < 6) {
+    const int f = threadIdx.x;
+    if (P.peer[f].active) {
+      const unsigned long long t0 = globaltimer_ns();
+      unsigned spins = 0;
+      while (ld_acquire_sys(P.flags_in + f) < P.level) {
+        if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > P.timeout_ns) {
+          atomicExch(P.status, 0x100u + (unsigned)f);   // watchdog: neighbour never arrived
+          break;
+        }
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ void shell_release_flags(const StepParams& P) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    const unsigned done = atomicAdd(P.shell_counter, 1u);
+    if (done == (unsigned)P.n_shell_ctas - 1u) {
+      *P.shell_counter = 0u;
+      __threadfence_system();
+      for (int f = 0; f < 6; ++f)
+        if (P.peer[f].active) st_release_sys(P.peer[f].flag, P.level + 1ull);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// TMA z-marching role
+// ---------------------------------------------------------------------------
+template <int TX, int RPT, int RG, int STAGES>
+struct TileCfg {
+  static constexpr int kTX = TX, kRPT = RPT, kRG = RG, kStages = STAGES;
+  static constexpr int kTY = RPT * RG;
+  static constexpr int kW = TX + 2;
+  static constexpr int kHaloRows = kTY + 2;
+  static constexpr int kConsumers = TX * RG;
+  static constexpr int kThreads = kConsumers + 32;
+  static constexpr int kHaloBytes = kW * kHaloRows * 8;
+  static constexpr int kHaloBytesPad = (kHaloBytes + 127) / 128 * 128;
+  static constexpr int kCoreBytes = TX * kTY * 8;
+  static constexpr int kStageBytes = kHaloBytesPad + kCoreBytes;
+  static constexpr int kBarBytes = 128 + 1024;   // barriers + reduction scratch
+  static constexpr int kSmemBytes = kBarBytes + STAGES * kStageBytes + 128;
+  static_assert(TX % 32 == 0 && TX <= 254, "TX must be a warp multiple and fit a TMA box");
+  static_assert(kHaloRows <= 256, "TMA box limit");
+  static_assert(2 * STAGES * 8 <= 128, "barrier area");
+};
+
+template <class Cfg>
+__device__ void tma_role(const StepParams& P, int work, uint8_t* smem, double& mx, double& s2) {
+  constexpr int TX = Cfg::kTX, RPT = Cfg::kRPT, STAGES = Cfg::kStages, W = Cfg::kW;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty = full + STAGES;
+  uint8_t* stage0 = smem + Cfg::kBarBytes;
+
+  const TileGeom& T = P.tile;
+  const int tx = work % T.ntx;
+  const int ty = (work / T.ntx) % T.nty;
+  const int ch = work / (T.ntx * T.nty);
+  const int x0 = T.lo[0] + tx * TX;
+  const int y0 = T.lo[1] + ty * Cfg::kTY;
+  const int z0 = T.lo[2] + ch * T.zc;
+  const int z1 = min(z0 + T.zc, T.hi[2]);
+  const int nzc = z1 - z0;
+  const int iters = nzc + 2;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, Cfg::kConsumers / 32);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5;
+  if (warp == Cfg::kConsumers / 32) {
+    // ===== producer warp: one lane drives TMA =====
+    if ((threadIdx.x & 31) == 0) {
+      tma_prefetch_desc(&P.map_halo);
+      tma_prefetch_desc(&P.map_core);
+      for (int t = 0; t < iters; ++t) {
+        const int s = t % STAGES;
+        const uint32_t ph = (uint32_t)(t / STAGES) & 1u;
+        mbar_wait(empty + s, ph ^ 1u);
+        const bool need_prev = (t >= 1 && t <= nzc);
+        uint8_t* st = stage0 + (size_t)s * Cfg::kStageBytes;
+        mbar_arrive_expect_tx(full + s, (uint32_t)(Cfg::kHaloBytes + (need_prev ? Cfg::kCoreBytes : 0)));
+        const int zz = z0 - 1 + t;
+        tma_load_3d(st, &P.map_halo, full + s, P.g.xoff + x0 - 1, y0 - 1, zz);
+        if (need_prev) tma_load_3d(st + Cfg::kHaloBytesPad, &P.map_core, full + s, P.g.xoff + x0, y0, zz);
+      }
+    }
+    return;   // callers re-converge all warps with __syncthreads() after this role
+  }
+
+  // ===== consumers =====
+  const int cxi = threadIdx.x % TX;           // column inside the tile
+  const int r0 = (threadIdx.x / TX) * RPT;    // first row of this thread
+  const int gx = x0 + cxi;                    // local x index
+  const bool x_ok = gx < T.hi[0];
+  const bool want_err = P.err.out != nullptr;
+  const double ct = P.ct_ptr ? __ldg(P.ct_ptr) : P.ct;
+  double acc[RPT], zm[RPT], sxy[RPT];
+  bool ok[RPT];
+  const double sxv = x_ok ? P.sx[gx] : 0.0;
+#pragma unroll
+  for (int r = 0; r < RPT; ++r) {
+    const int gy = y0 + r0 + r;
+    ok[r] = x_ok && gy < T.hi[1];
+    sxy[r] = ok[r] ? sxv * P.sy[gy] : 0.0;
+    acc[r] = 0.0;
+    zm[r] = 0.0;
+  }
+  double* out_col = P.nxt + (long long)(y0 + r0) * P.g.pitch + P.g.xoff + gx;
+
+  for (int t = 0; t < iters; ++t) {
+    const int s = t % STAGES;
+    const uint32_t ph = (uint32_t)(t / STAGES) & 1u;
+    mbar_wait(full + s, ph);
+    const double* cs = reinterpret_cast<const double*>(stage0 + (size_t)s * Cfg::kStageBytes);
+    const double* ps = reinterpret_cast<const double*>(stage0 + (size_t)s * Cfg::kStageBytes + Cfg::kHaloBytesPad);
+    double col[RPT + 2];
+#pragma unroll
+    for (int q = 0; q < RPT + 2; ++q) col[q] = cs[(r0 + q) * W + cxi + 1];
+
+    if (t >= 2) {
+      // plane zo = z0 + t - 2 is complete: add the z+1 neighbour, store, fold the error
+      const int zo = z0 + t - 2;
+      double* o = out_col + (long long)zo * P.g.plane;
+      const double szt = want_err ? P.sz[zo] * ct : 0.0;
+#pragma unroll
+      for (int r = 0; r < RPT; ++r) {
+        const double v = w3d_finish(acc[r], col[r + 1], P.cz);
+        if (ok[r]) {
+          o[(long long)r * P.g.pitch] = v;
+          if (want_err) {
+            const double e = w3d_abs_err(v, sxy[r], szt);
+            mx = fmax(mx, e);
+            s2 = fma(e, e, s2);
+          }
+        }
+      }
+    }
+    if (t >= 1 && t <= nzc) {
+#pragma unroll
+      for (int r = 0; r < RPT; ++r) {
+        const double xm = cs[(r0 + r + 1) * W + cxi];
+        const double xp = cs[(r0 + r + 1) * W + cxi + 2];
+        const double pv = ps[(r0 + r) * TX + cxi];
+        acc[r] = w3d_partial(col[r + 1], pv, xm, xp, col[r], col[r + 2], zm[r], P.a, P.b, P.cx, P.cy, P.cz);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) zm[r] = col[r + 1];
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(empty + s);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// kernels
+// ---------------------------------------------------------------------------
+template <class Cfg, int MINB>
+__global__ void __launch_bounds__(Cfg::kThreads, MINB)
+fused_step_kernel(const __grid_constant__ StepParams P) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  double* red = reinterpret_cast<double*>(smem + 128);
+  double mx = 0.0, s2 = 0.0;
+  if ((int)blockIdx.x < P.n_shell_ctas) {
+    if (P.use_flags) shell_wait_flags(P);
+    const long long nthreads = (long long)P.n_shell_ctas * blockDim.x;
+    shell_compute(P, (long long)blockIdx.x * blockDim.x + threadIdx.x, nthreads, P.use_flags != 0, mx, s2);
+    if (P.use_flags) shell_release_flags(P);
+  } else {
+    tma_role<Cfg>(P, (int)blockIdx.x - P.n_shell_ctas, smem, mx, s2);
+  }
+  if (P.err.out != nullptr) {
+    __syncthreads();
+    publish_error(P.err, mx, s2, red);
+  }
+}
+
+// plain one-thread-per-node kernel over the box table (no communication)
+__global__ void __launch_bounds__(256) box_step_kernel(const __grid_constant__ StepParams P) {
+  __shared__ double red[66];
+  double mx = 0.0, s2 = 0.0;
+  shell_compute(P, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x,
+                false, mx, s2);
+  publish_error(P.err, mx, s2, red);
+}
+
+// K1: analytic layer 0 on every node (ghosts and row padding included)
+__global__ void __launch_bounds__(256) init_kernel(double* u, Geometry g, const double* sx,
+                                                   const double* sy, const double* sz) {
+  const long long rows = (long long)(g.n[1] + 2) * (g.n[2] + 2);
+  const long long total = rows * g.pitch;
+  for (long long id = (long long)blockIdx.x * blockDim.x + threadIdx.x; id < total;
+       id += (long long)gridDim.x * blockDim.x) {
+    const int xe = (int)(id % g.pitch);
+    const long long row = id / g.pitch;
+    const int j = (int)(row % (g.n[1] + 2));
+    const int k = (int)(row / (g.n[1] + 2));
+    const int i = xe - g.xoff;
+    double v = 0.0;
+    if (i >= 0 && i <= g.n[0] + 1) v = sx[i] * (sy[j] * sz[k]);
+    u[id] = v;
+  }
+}
+
+// K6 stand-alone: error norms of a field
+__global__ void __launch_bounds__(256) error_kernel(const double* u, Geometry g, const double* sx,
+                                                    const double* sy, const double* sz, double ct,
+                                                    ErrCtl e) {
+  __shared__ double red[66];
+  double mx = 0.0, s2 = 0.0;
+  const long long rows = (long long)g.n[1] * g.n[2];
+  // one warp per row keeps loads coalesced
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = warp0; r < rows; r += nwarps) {
+    const int j = 1 + (int)(r % g.n[1]);
+    const int k = 1 + (int)(r / g.n[1]);
+    const double* row = u + gidx(g, 0, j, k);
+    const double syj = sy[j], szt = sz[k] * ct;
+    for (int i = 1 + lane; i <= g.n[0]; i += 32) {
+      const double e1 = w3d_abs_err(row[i], sx[i] * syj, szt);
+      mx = fmax(mx, e1);
+      s2 = fma(e1, e1, s2);
+    }
+  }
+  publish_error(e, mx, s2, red);
+}
+
+// K5 (baseline only): face pack / unpack.  layer = index along `axis` to read/write.
+__global__ void __launch_bounds__(256) face_kernel(double* u, Geometry g, int axis, int layer,
+                                                   double* buf, int unpack) {
+  const int a = (axis + 1) % 3, c = (axis + 2) % 3;   // same enumeration as the CPU library
+  // buffer order: fastest index first over the two other axes in (x,y,z) order
+  int f0, f1;   // fast, slow axes
+  if (axis == 0) { f0 = 1; f1 = 2; } else if (axis == 1) { f0 = 0; f1 = 2; } else { f0 = 0; f1 = 1; }
+  (void)a; (void)c;
+  const long long total = (long long)g.n[f0] * g.n[f1];
+  for (long long id = (long long)blockIdx.x * blockDim.x + threadIdx.x; id < total;
+       id += (long long)gridDim.x * blockDim.x) {
+    int q[3];
+    q[axis] = layer;
+    q[f0] = 1 + (int)(id % g.n[f0]);
+    q[f1] = 1 + (int)(id / g.n[f0]);
+    const long long o = gidx(g, q[0], q[1], q[2]);
+    if (unpack) u[o] = buf[id]; else buf[id] = u[o];
+  }
+}
+
+// periodic self-wrap of one axis: ghost <- opposite edge, for both sides
+__global__ void __launch_bounds__(256) wrap_kernel(double* u, Geometry g, int axis) {
+  int f0, f1;
+  if (axis == 0) { f0 = 1; f1 = 2; } else if (axis == 1) { f0 = 0; f1 = 2; } else { f0 = 0; f1 = 1; }
+  const int e0 = g.n[f0] + 2, e1 = g.n[f1] + 2;   // ghosts of the other axes too
+  const long long total = (long long)e0 * e1;
+  for (long long id = (long long)blockIdx.x * blockDim.x + threadIdx.x; id < total;
+       id += (long long)gridDim.x * blockDim.x) {
+    int q[3];
+    q[f0] = (int)(id % e0);
+    q[f1] = (int)(id / e0);
+    q[axis] = g.n[axis];
+    const double hi = u[gidx(g, q[0], q[1], q[2])];
+    q[axis] = 1;
+    const double lo = u[gidx(g, q[0], q[1], q[2])];
+    q[axis] = 0;
+    u[gidx(g, q[0], q[1], q[2])] = hi;
+    q[axis] = g.n[axis] + 1;
+    u[gidx(g, q[0], q[1], q[2])] = lo;
+  }
+}
+
+}  // namespace w3d

@@ -1,0 +1,461 @@
+// wave_api.cu — host side of libwave3d_b200.so: plans, tensor maps, launch
+// geometry and the extern "C" entry points declared in include/wave3d.h.
+//
+// Replaces the host half of the reference's mpigpu-1.cu (report.pdf p.14-17 §4):
+// there, every step staged halos D2H -> MPI_Sendrecv -> H2D; here
+// a step is one kernel launch and nothing crosses the host.
+#include "kernels.cuh"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+using namespace w3d;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CUDA_TRY(x)                                                                      \
+  do {                                                                                   \
+    cudaError_t e_ = (x);                                                                \
+    if (e_ != cudaSuccess) return fail(W3D_ECUDA, "%s: %s", #x, cudaGetErrorString(e_)); \
+  } while (0)
+
+// ---- TMA tile variants ------------------------------------------------------------
+//            TX  RPT RG STAGES
+using Cfg0 = TileCfg<128, 8, 1, 4>;   // 128 x 8 tile, 160 threads, ~75 KB  -> 3 CTAs / SM
+using Cfg1 = TileCfg<128, 8, 2, 3>;   // 128 x 16 tile, 288 threads, ~105 KB -> 2 CTAs / SM
+using Cfg2 = TileCfg<128, 8, 4, 3>;   // 128 x 32 tile, 544 threads, ~204 KB -> 1 CTA / SM
+using Cfg3 = TileCfg<64, 8, 4, 4>;    // 64 x 32 tile, 288 threads, ~140 KB  -> 1 CTA / SM
+
+struct Variant {
+  int tx, ty, threads, smem, ctas_per_sm;
+  void (*kernel)(const StepParams);
+  const char* name;
+};
+
+const Variant kVariants[] = {
+    {Cfg0::kTX, Cfg0::kTY, Cfg0::kThreads, Cfg0::kSmemBytes, 3, fused_step_kernel<Cfg0, 3>, "128x8x4st"},
+    {Cfg1::kTX, Cfg1::kTY, Cfg1::kThreads, Cfg1::kSmemBytes, 2, fused_step_kernel<Cfg1, 2>, "128x16x3st"},
+    {Cfg2::kTX, Cfg2::kTY, Cfg2::kThreads, Cfg2::kSmemBytes, 1, fused_step_kernel<Cfg2, 1>, "128x32x3st"},
+    {Cfg3::kTX, Cfg3::kTY, Cfg3::kThreads, Cfg3::kSmemBytes, 1, fused_step_kernel<Cfg3, 1>, "64x32x4st"},
+};
+constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
+constexpr int kDefaultVariant = 1;
+
+// ---- workspace layout ---------------------------------------------------------------
+constexpr size_t kCounterBytes = 256;   // tickets [0..7] at 0, shell counter at +64
+constexpr size_t kSlotBytes = 2ull * W3D_MAX_PARTIALS * sizeof(double);
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+}  // namespace
+
+struct W3dPlan {
+  W3dPlanDesc d;
+  Geometry g;
+  int variant;
+  int num_sms;
+  CUtensorMap halo[2], core[2];    // per field array
+  bool maps_ok;
+  // fused geometry
+  int ilo[3], ihi[3];
+  BoxTable shell;
+  int n_shell_ctas;
+  TileGeom tile;                   // interior
+  bool any_peer;
+  const double* ct_table;          // optional device table of cos(a_t t_n), host-fed
+  long long launches;
+  char text[768];
+};
+
+namespace {
+
+ErrCtl err_ctl(const W3dPlan* p, int slot, double* out) {
+  ErrCtl e;
+  char* ws = static_cast<char*>(p->d.workspace);
+  e.out = out;
+  e.ticket = reinterpret_cast<unsigned*>(ws) + slot;
+  e.part_max = reinterpret_cast<double*>(ws + kCounterBytes + (size_t)slot * kSlotBytes);
+  e.part_sum = e.part_max + W3D_MAX_PARTIALS;
+  return e;
+}
+
+int encode_maps(W3dPlan* p) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled is not available from the driver");
+  const Variant& v = kVariants[p->variant];
+  const cuuint64_t dims[3] = {(cuuint64_t)p->g.pitch, (cuuint64_t)(p->g.n[1] + 2), (cuuint64_t)(p->g.n[2] + 2)};
+  const cuuint64_t strides[2] = {(cuuint64_t)p->g.pitch * 8, (cuuint64_t)p->g.plane * 8};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  for (int f = 0; f < 2; ++f) {
+    const cuuint32_t hb[3] = {(cuuint32_t)(v.tx + 2), (cuuint32_t)(v.ty + 2), 1};
+    const cuuint32_t cb[3] = {(cuuint32_t)v.tx, (cuuint32_t)v.ty, 1};
+    CUresult r = enc(&p->halo[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, p->d.field[f], dims, strides, hb, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled(halo) failed: %d", (int)r);
+    r = enc(&p->core[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, p->d.field[f], dims, strides, cb, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled(core) failed: %d", (int)r);
+  }
+  p->maps_ok = true;
+  return W3D_OK;
+}
+
+// pick planes-per-CTA so that the CTA count fills whole waves of the resident slots
+void plan_tiles(const W3dPlan* p, const int lo[3], const int hi[3], int zchunk, TileGeom* t) {
+  const Variant& v = kVariants[p->variant];
+  for (int d = 0; d < 3; ++d) { t->lo[d] = lo[d]; t->hi[d] = hi[d]; }
+  const int ex = std::max(0, hi[0] - lo[0]), ey = std::max(0, hi[1] - lo[1]), ez = std::max(0, hi[2] - lo[2]);
+  t->ntx = (ex + v.tx - 1) / v.tx;
+  t->nty = (ey + v.ty - 1) / v.ty;
+  if (ex == 0 || ey == 0 || ez == 0) { t->ntx = t->nty = 0; t->zc = 1; t->nchunks = 0; return; }
+  const long long tiles = (long long)t->ntx * t->nty;
+  if (zchunk > 0) {
+    t->zc = std::min(zchunk, ez);
+  } else {
+    const long long slots = (long long)p->num_sms * v.ctas_per_sm;
+    double best = 1e300;
+    int best_c = 1;
+    const int cmax = std::max(1, ez / 16);
+    for (int c = 1; c <= cmax; ++c) {
+      const int zc = (ez + c - 1) / c;
+      const long long ctas = tiles * ((ez + zc - 1) / zc);
+      if (ctas > W3D_MAX_PARTIALS - 1024) break;
+      const long long waves = (ctas + slots - 1) / slots;
+      // per-CTA cost: zc planes + 2 halo planes (read only, ~1/3 of the traffic) + launch/drain
+      const double cost = (double)waves * (zc + 2.0 / 3.0 + 1.5);
+      if (cost < best - 1e-9) { best = cost; best_c = c; }
+    }
+    t->zc = (ez + best_c - 1) / best_c;
+  }
+  t->nchunks = (ez + t->zc - 1) / t->zc;
+}
+
+void add_box(BoxTable* B, const int lo[3], const int hi[3]) {
+  for (int d = 0; d < 3; ++d)
+    if (hi[d] <= lo[d]) return;
+  const int b = B->nboxes++;
+  long long cnt = 1;
+  for (int d = 0; d < 3; ++d) {
+    B->lo[b][d] = lo[d];
+    B->ext[b][d] = hi[d] - lo[d];
+    cnt *= B->ext[b][d];
+  }
+  B->prefix[b + 1] = B->prefix[b] + cnt;
+}
+
+void fill_common(const W3dPlan* p, StepParams* P, int s, double a, double b, double cscale, double ct) {
+  std::memset(P, 0, sizeof(*P));
+  const int cur = s & 1, nxt = cur ^ 1;
+  P->map_halo = p->halo[cur];
+  P->map_core = p->core[nxt];
+  P->g = p->g;
+  P->cur = p->d.field[cur];
+  P->nxt = p->d.field[nxt];
+  P->sx = p->d.tab[0];
+  P->sy = p->d.tab[1];
+  P->sz = p->d.tab[2];
+  P->a = a;
+  P->b = b;
+  P->cx = cscale * p->d.coef[0];
+  P->cy = cscale * p->d.coef[1];
+  P->cz = cscale * p->d.coef[2];
+  P->ct = ct;
+  P->ct_ptr = p->ct_table ? p->ct_table + (s + 1) : nullptr;
+  P->status = p->d.status;
+  P->level = (unsigned long long)s;
+  P->timeout_ns = (unsigned long long)(p->d.spin_timeout_ms > 0 ? p->d.spin_timeout_ms : 10000) * 1000000ull;
+}
+
+int launch_fused(W3dPlan* p, const StepParams& P, int nblocks, cudaStream_t st) {
+  const Variant& v = kVariants[p->variant];
+  if (nblocks <= 0) return W3D_OK;
+  if (nblocks > W3D_MAX_PARTIALS) return fail(W3D_EINVAL, "launch of %d CTAs exceeds W3D_MAX_PARTIALS", nblocks);
+  v.kernel<<<nblocks, v.threads, v.smem, st>>>(P);
+  CUDA_TRY(cudaGetLastError());
+  ++p->launches;
+  return W3D_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* w3d_last_error(void) { return g_err; }
+const char* w3d_version(void) { return "wave3d-b200 1.0 (sm_100a)"; }
+size_t w3d_workspace_bytes(void) { return kCounterBytes + (size_t)W3D_ERR_SLOTS * kSlotBytes; }
+size_t w3d_error_workspace_bytes(void) { return kCounterBytes + kSlotBytes; }
+
+int64_t w3d_pitch_for(int32_t nx) {
+  const int64_t need = (int64_t)W3D_XOFF + nx + 2;
+  return (need + W3D_PITCH_ALIGN - 1) / W3D_PITCH_ALIGN * W3D_PITCH_ALIGN;
+}
+
+int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
+  if (!desc || !out) return fail(W3D_EINVAL, "null argument");
+  const W3dBlock& b = desc->blk;
+  if (b.n[0] < 1 || b.n[1] < 1 || b.n[2] < 1) return fail(W3D_EINVAL, "empty block");
+  if (b.pitch % 2 != 0 || b.pitch < b.xoff + b.n[0] + 2 || b.xoff < 1)
+    return fail(W3D_EINVAL, "bad layout: pitch=%lld xoff=%d nx=%d (pitch must be even and >= xoff+nx+2, xoff >= 1)",
+                (long long)b.pitch, b.xoff, b.n[0]);
+  if (!desc->field[0] || !desc->field[1] || !desc->tab[0] || !desc->tab[1] || !desc->tab[2])
+    return fail(W3D_EINVAL, "null field or table pointer");
+  if ((reinterpret_cast<uintptr_t>(desc->field[0]) | reinterpret_cast<uintptr_t>(desc->field[1])) & 15)
+    return fail(W3D_EINVAL, "field arrays must be 16-byte aligned");
+  if (!desc->workspace || desc->workspace_bytes < w3d_workspace_bytes())
+    return fail(W3D_EINVAL, "workspace too small: need %zu bytes", w3d_workspace_bytes());
+  if (!desc->status || !desc->flags_in) return fail(W3D_EINVAL, "status / flags_in must be provided");
+  W3dPlan* p = new (std::nothrow) W3dPlan();
+  if (!p) return fail(W3D_ENOMEM, "out of host memory");
+  p->d = *desc;
+  p->g.n[0] = b.n[0]; p->g.n[1] = b.n[1]; p->g.n[2] = b.n[2];
+  p->g.xoff = b.xoff;
+  p->g.pitch = b.pitch;
+  p->g.plane = (long long)(b.n[1] + 2) * b.pitch;
+  p->variant = desc->variant >= 0 && desc->variant < kNumVariants ? desc->variant : kDefaultVariant;
+  p->num_sms = desc->num_sms;
+  if (p->num_sms <= 0) {
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    p->num_sms = sms;
+  }
+  p->maps_ok = false;
+  p->launches = 0;
+  p->ct_table = nullptr;
+  // interior / shell split
+  p->any_peer = false;
+  for (int d = 0; d < 3; ++d) {
+    p->ilo[d] = 1 + (desc->peer[d * 2].active ? 1 : 0);
+    p->ihi[d] = std::max(p->ilo[d], b.n[d] + 1 - (desc->peer[d * 2 + 1].active ? 1 : 0));
+    p->any_peer = p->any_peer || desc->peer[d * 2].active || desc->peer[d * 2 + 1].active;
+  }
+  std::memset(&p->shell, 0, sizeof(p->shell));
+  {
+    int lo[3] = {1, 1, 1}, hi[3] = {b.n[0] + 1, b.n[1] + 1, b.n[2] + 1};
+    for (int d = 2; d >= 0; --d) {
+      int l2[3] = {lo[0], lo[1], lo[2]}, h2[3] = {hi[0], hi[1], hi[2]};
+      if (p->ilo[d] > lo[d]) { h2[d] = p->ilo[d]; add_box(&p->shell, l2, h2); h2[d] = hi[d]; }
+      if (p->ihi[d] < hi[d]) { l2[d] = p->ihi[d]; add_box(&p->shell, l2, h2); }
+      lo[d] = p->ilo[d];
+      hi[d] = p->ihi[d];
+    }
+  }
+  const Variant& v = kVariants[p->variant];
+  const long long shell_nodes = p->shell.prefix[p->shell.nboxes];
+  p->n_shell_ctas = shell_nodes == 0 ? 0
+      : (int)std::min<long long>((shell_nodes + (long long)v.threads * 4 - 1) / ((long long)v.threads * 4),
+                                 (long long)p->num_sms * 2);
+  plan_tiles(p, p->ilo, p->ihi, desc->zchunk, &p->tile);
+  cudaError_t e = cudaFuncSetAttribute(v.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v.smem);
+  if (e != cudaSuccess) {
+    delete p;
+    return fail(W3D_ECUDA, "cudaFuncSetAttribute(smem=%d): %s", v.smem, cudaGetErrorString(e));
+  }
+  int rc = encode_maps(p);
+  if (rc != W3D_OK) { delete p; return rc; }
+  snprintf(p->text, sizeof(p->text),
+           "block %dx%dx%d pitch %lld | variant %s (%d thr, %d B smem, %d CTA/SM) | interior [%d,%d)x[%d,%d)x[%d,%d) "
+           "tiles %dx%d zc %d chunks %d -> %lld CTAs | shell %lld nodes in %d boxes, %d CTAs | SMs %d",
+           b.n[0], b.n[1], b.n[2], (long long)b.pitch, v.name, v.threads, v.smem, v.ctas_per_sm, p->ilo[0], p->ihi[0],
+           p->ilo[1], p->ihi[1], p->ilo[2], p->ihi[2], p->tile.ntx, p->tile.nty, p->tile.zc, p->tile.nchunks,
+           (long long)p->tile.ntx * p->tile.nty * p->tile.nchunks, shell_nodes, p->shell.nboxes, p->n_shell_ctas,
+           p->num_sms);
+  *out = p;
+  return W3D_OK;
+}
+
+void w3d_plan_destroy(W3dPlan* plan) { delete plan; }
+int w3d_plan_set_ct_table(W3dPlan* plan, const double* dev_table) {
+  if (!plan) return fail(W3D_EINVAL, "null plan");
+  plan->ct_table = dev_table;
+  return W3D_OK;
+}
+const char* w3d_plan_describe(W3dPlan* plan) { return plan ? plan->text : ""; }
+long long w3d_plan_launches(W3dPlan* plan) { return plan ? plan->launches : 0; }
+
+int w3d_plan_init(W3dPlan* p, void* stream) {
+  if (!p) return fail(W3D_EINVAL, "null plan");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long total = (long long)(p->g.n[2] + 2) * p->g.plane;
+  const int blocks = (int)std::min<long long>((total + 255) / 256, (long long)p->num_sms * 16);
+  init_kernel<<<blocks, 256, 0, st>>>(p->d.field[0], p->g, p->d.tab[0], p->d.tab[1], p->d.tab[2]);
+  CUDA_TRY(cudaGetLastError());
+  ++p->launches;
+  CUDA_TRY(cudaMemsetAsync(p->d.field[1], 0, (size_t)total * sizeof(double), st));
+  CUDA_TRY(cudaMemsetAsync(p->d.flags_in, 0, 6 * sizeof(unsigned long long), st));
+  CUDA_TRY(cudaMemsetAsync(p->d.status, 0, sizeof(uint32_t), st));
+  CUDA_TRY(cudaMemsetAsync(p->d.workspace, 0, kCounterBytes, st));
+  return W3D_OK;
+}
+
+int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double ct, double* err_out,
+                   void* stream) {
+  if (!p) return fail(W3D_EINVAL, "null plan");
+  StepParams P;
+  fill_common(p, &P, s, a, b, cscale, ct);
+  P.err = err_ctl(p, 0, err_out);
+  P.tile = p->tile;
+  P.boxes = p->shell;
+  P.n_shell_ctas = p->n_shell_ctas;
+  P.use_flags = p->any_peer ? 1 : 0;
+  const int nxt = (s & 1) ^ 1;
+  for (int f = 0; f < 6; ++f) {
+    const W3dPeer& q = p->d.peer[f];
+    P.peer[f].active = q.active;
+    P.peer[f].ghost_index = q.ghost_index;
+    P.peer[f].field = q.field[nxt];
+    P.peer[f].pitch = q.pitch;
+    P.peer[f].plane = q.plane;
+    P.peer[f].flag = q.flag;
+  }
+  P.flags_in = p->d.flags_in;
+  P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
+  const int nblocks = p->n_shell_ctas + p->tile.ntx * p->tile.nty * p->tile.nchunks;
+  return launch_fused(p, P, nblocks, static_cast<cudaStream_t>(stream));
+}
+
+int w3d_step_tma(W3dPlan* p, int s, double a, double b, double cscale, double ct, const int32_t lo[3],
+                 const int32_t hi[3], double* err_out, int slot, void* stream) {
+  if (!p) return fail(W3D_EINVAL, "null plan");
+  if (slot < 0 || slot >= W3D_ERR_SLOTS) return fail(W3D_EINVAL, "bad slot %d", slot);
+  StepParams P;
+  fill_common(p, &P, s, a, b, cscale, ct);
+  P.err = err_ctl(p, slot, err_out);
+  int l[3], h[3];
+  for (int d = 0; d < 3; ++d) {
+    l[d] = lo ? lo[d] : 1;
+    h[d] = hi ? hi[d] : p->g.n[d] + 1;
+    if (l[d] < 1 || h[d] > p->g.n[d] + 1) return fail(W3D_EINVAL, "box outside the block");
+  }
+  plan_tiles(p, l, h, p->d.zchunk, &P.tile);
+  P.n_shell_ctas = 0;
+  P.use_flags = 0;
+  const int nblocks = P.tile.ntx * P.tile.nty * P.tile.nchunks;
+  if (nblocks == 0 && err_out) {
+    CUDA_TRY(cudaMemsetAsync(err_out, 0, 2 * sizeof(double), static_cast<cudaStream_t>(stream)));
+    return W3D_OK;
+  }
+  return launch_fused(p, P, nblocks, static_cast<cudaStream_t>(stream));
+}
+
+int w3d_step_box(W3dPlan* p, int s, double a, double b, double cscale, double ct, const int32_t lo[3],
+                 const int32_t hi[3], double* err_out, int slot, void* stream) {
+  if (!p) return fail(W3D_EINVAL, "null plan");
+  if (slot < 0 || slot >= W3D_ERR_SLOTS) return fail(W3D_EINVAL, "bad slot %d", slot);
+  StepParams P;
+  fill_common(p, &P, s, a, b, cscale, ct);
+  P.err = err_ctl(p, slot, err_out);
+  int l[3], h[3];
+  for (int d = 0; d < 3; ++d) {
+    l[d] = lo ? lo[d] : 1;
+    h[d] = hi ? hi[d] : p->g.n[d] + 1;
+    if (l[d] < 1 || h[d] > p->g.n[d] + 1) return fail(W3D_EINVAL, "box outside the block");
+  }
+  add_box(&P.boxes, l, h);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long nodes = P.boxes.prefix[P.boxes.nboxes];
+  if (nodes == 0) {
+    if (err_out) CUDA_TRY(cudaMemsetAsync(err_out, 0, 2 * sizeof(double), st));
+    return W3D_OK;
+  }
+  const int blocks = (int)std::min<long long>((nodes + 255) / 256, (long long)W3D_MAX_PARTIALS);
+  box_step_kernel<<<blocks, 256, 0, st>>>(P);
+  CUDA_TRY(cudaGetLastError());
+  ++p->launches;
+  return W3D_OK;
+}
+
+static int face_layer(const W3dPlan* p, int axis, int side, int ghost) {
+  const int n = p->g.n[axis];
+  return side == 0 ? (ghost ? 0 : 1) : (ghost ? n + 1 : n);
+}
+
+int w3d_pack_face(W3dPlan* p, int parity, int axis, int side, int ghost, double* buf, void* stream) {
+  if (!p || !buf || axis < 0 || axis > 2) return fail(W3D_EINVAL, "bad argument");
+  const int f0 = axis == 0 ? 1 : 0, f1 = axis == 2 ? 1 : 2;
+  const long long total = (long long)p->g.n[f0] * p->g.n[f1];
+  const int blocks = (int)std::min<long long>((total + 255) / 256, 4096);
+  face_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(p->d.field[parity & 1], p->g, axis,
+                                                                   face_layer(p, axis, side, ghost), buf, 0);
+  CUDA_TRY(cudaGetLastError());
+  ++p->launches;
+  return W3D_OK;
+}
+
+int w3d_unpack_face(W3dPlan* p, int parity, int axis, int side, int ghost, const double* buf, void* stream) {
+  if (!p || !buf || axis < 0 || axis > 2) return fail(W3D_EINVAL, "bad argument");
+  const int f0 = axis == 0 ? 1 : 0, f1 = axis == 2 ? 1 : 2;
+  const long long total = (long long)p->g.n[f0] * p->g.n[f1];
+  const int blocks = (int)std::min<long long>((total + 255) / 256, 4096);
+  face_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      p->d.field[parity & 1], p->g, axis, face_layer(p, axis, side, ghost), const_cast<double*>(buf), 1);
+  CUDA_TRY(cudaGetLastError());
+  ++p->launches;
+  return W3D_OK;
+}
+
+int w3d_wrap_axis(W3dPlan* p, int parity, int axis, void* stream) {
+  if (!p || axis < 0 || axis > 2) return fail(W3D_EINVAL, "bad argument");
+  const int f0 = axis == 0 ? 1 : 0, f1 = axis == 2 ? 1 : 2;
+  const long long total = (long long)(p->g.n[f0] + 2) * (p->g.n[f1] + 2);
+  const int blocks = (int)std::min<long long>((total + 255) / 256, 4096);
+  wrap_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(p->d.field[parity & 1], p->g, axis);
+  CUDA_TRY(cudaGetLastError());
+  ++p->launches;
+  return W3D_OK;
+}
+
+int w3d_error_norms(const double* u, const W3dBlock* blk, const double* sx, const double* sy,
+                    const double* sz, double ct, double* out, void* workspace, size_t workspace_bytes,
+                    void* stream) {
+  if (!u || !blk || !sx || !sy || !sz || !out || !workspace) return fail(W3D_EINVAL, "null argument");
+  if (workspace_bytes < w3d_error_workspace_bytes())
+    return fail(W3D_EINVAL, "workspace too small: need %zu bytes", w3d_error_workspace_bytes());
+  Geometry g;
+  g.n[0] = blk->n[0]; g.n[1] = blk->n[1]; g.n[2] = blk->n[2];
+  g.xoff = blk->xoff;
+  g.pitch = blk->pitch;
+  g.plane = (long long)(blk->n[1] + 2) * blk->pitch;
+  ErrCtl e;
+  char* ws = static_cast<char*>(workspace);
+  e.out = out;
+  e.ticket = reinterpret_cast<unsigned*>(ws);
+  e.part_max = reinterpret_cast<double*>(ws + kCounterBytes);
+  e.part_sum = e.part_max + W3D_MAX_PARTIALS;
+  const long long rows = (long long)g.n[1] * g.n[2];
+  const int blocks = (int)std::max<long long>(1, std::min<long long>((rows + 7) / 8, 148 * 8));
+  error_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(u, g, sx, sy, sz, ct, e);
+  CUDA_TRY(cudaGetLastError());
+  return W3D_OK;
+}
+
+}  // extern "C"

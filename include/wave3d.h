@@ -1,0 +1,134 @@
+/* wave3d.h — C ABI of the sm_100a CUDA library (libwave3d_b200.so).
+ *
+ * B200-native replacement for the reference's MPI+CUDA program mpigpu-1.cu
+ * (named at readme.md:68, described in report.pdf p.14-17 §4; not shipped).
+ * Functional kernel inventory of that program -> entry points here
+ * (SURVEY.md §2.6):
+ *   K1 init layer 0                      -> w3d_plan_init
+ *   K2 Taylor step, K3 leapfrog, K4 BCs  -> w3d_step_fused / w3d_step_tma / w3d_step_box
+ *   K5 halo pack/unpack + MPI_Sendrecv   -> in-kernel NVLink P2P stores + flags (w3d_step_fused);
+ *                                           w3d_pack_face / w3d_unpack_face for the NCCL baseline
+ *   K6 error kernel + MPI_Reduce         -> epilogue of every step kernel; w3d_error_norms stand-alone
+ *
+ * All pointers are device pointers unless stated.  Every function returns 0 on
+ * success or a negative W3D_E* code; w3d_last_error() gives the text.  Streams are
+ * passed as void* (cudaStream_t).  No function synchronises the device.
+ */
+#ifndef WAVE3D_H
+#define WAVE3D_H
+#include <stddef.h>
+#include <stdint.h>
+#include "wave3d_cpu.h" /* W3dBlock: the block layout is shared with the CPU library */
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define W3D_OK 0
+#define W3D_EINVAL (-1)
+#define W3D_ECUDA (-2)
+#define W3D_ENOMEM (-3)
+#define W3D_EDRIVER (-4)
+
+#define W3D_XOFF 15          /* x ghost sits at element 15, first unknown at 16 (128 B aligned) */
+#define W3D_PITCH_ALIGN 16   /* row pitch is a multiple of 16 doubles (128 B) */
+#define W3D_ERR_SLOTS 8      /* independent error-reduction slots per step */
+#define W3D_MAX_PARTIALS 16384
+
+/* Recommended layout for n unknowns along x. */
+int64_t w3d_pitch_for(int32_t nx);
+
+/* One face of the block whose edge layer must be delivered to a neighbour's ghost
+ * layer (the neighbour may be this rank itself for a periodic axis on one rank). */
+typedef struct W3dPeer {
+  int32_t active;        /* 0: Dirichlet boundary, nothing to send */
+  int32_t ghost_index;   /* index along the face axis of the peer's ghost layer that my edge fills */
+  double* field[2];      /* peer's two field arrays, mapped into this process */
+  int64_t pitch;         /* peer's row pitch (elements) */
+  int64_t plane;         /* peer's plane stride (elements) */
+  unsigned long long* flag;   /* peer's incoming flag word for this face (I write it) */
+  unsigned long long* err_slot; /* unused, reserved */
+} W3dPeer;
+
+typedef struct W3dPlanDesc {
+  W3dBlock blk;
+  double* field[2];             /* my two field arrays (time levels alternate) */
+  const double* tab[3];         /* analytic tables sx, sy, sz with n+2 entries (ghosts incl.) */
+  double coef[3];               /* tau^2 / h_d^2 */
+  W3dPeer peer[6];              /* index axis*2 + side */
+  unsigned long long* flags_in; /* 6 words written by my neighbours: level of the ghost data present */
+  uint32_t* status;             /* device word, set non-zero by the spin watchdog */
+  void* workspace;              /* scratch for the error reductions and shell counters */
+  size_t workspace_bytes;       /* >= w3d_workspace_bytes() */
+  int32_t variant;              /* TMA tile variant, -1 = auto */
+  int32_t zchunk;               /* planes per CTA in the z-marching kernel, 0 = auto */
+  int32_t num_sms;              /* 0 = query the current device */
+  int32_t spin_timeout_ms;      /* watchdog for flag waits, 0 = 2000 */
+} W3dPlanDesc;
+
+typedef struct W3dPlan W3dPlan;
+
+size_t w3d_workspace_bytes(void);
+const char* w3d_last_error(void);
+const char* w3d_version(void);
+
+int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out);
+void w3d_plan_destroy(W3dPlan* plan);
+/* Human-readable description of the launch geometry chosen (static storage). */
+const char* w3d_plan_describe(W3dPlan* plan);
+/* Number of kernel launches issued through this plan so far. */
+long long w3d_plan_launches(W3dPlan* plan);
+
+/* Optional: read the time factor cos(a_t t_{s+1}) of step s from dev_table[s+1] (device
+ * memory that the host refreshes every step) instead of the by-value `ct` argument.
+ * NULL switches back.  Used by the streaming / end-to-end mode. */
+int w3d_plan_set_ct_table(W3dPlan* plan, const double* dev_table);
+
+/* field[0] <- analytic u0 on every node incl. ghosts, field[1] <- 0; clears flags,
+ * status and workspace counters (K1; report.pdf p.5 §2.2 item 1). */
+int w3d_plan_init(W3dPlan* plan, void* stream);
+
+/* One time step producing level s+1 from levels s (cur = field[s&1]) and s-1
+ * (stored in field[(s+1)&1], overwritten in place):
+ *    next = a*cur + b*prev + cscale * sum_d coef[d] * (cur_{+1} - 2 cur + cur_{-1})
+ * Taylor first step: a=1,b=0,cscale=0.5; leapfrog: a=2,b=-1,cscale=1.
+ * If err_out != NULL the kernel also reduces max|next - exact| and sum (..)^2 over
+ * the nodes it updates into err_out[0..1] (exact = sx*sy*sz*ct), using reduction
+ * slot `slot` of the workspace.
+ *
+ * w3d_step_fused: ONE launch.  CTAs with low block indices compute the shell
+ *   (nodes adjacent to a face with a neighbour) after acquiring the neighbours'
+ *   flags for level s, store the results locally and straight into the
+ *   neighbours' ghost layers (NVLink P2P), and the last shell CTA releases the
+ *   flags for level s+1; the remaining CTAs stream the interior with TMA.
+ * w3d_step_tma: the TMA z-marching kernel on the box [lo,hi) only, no communication.
+ * w3d_step_box: the plain one-thread-per-node kernel on the box [lo,hi), no
+ *   communication (used by the NCCL baseline for the shell and as a numerics check). */
+int w3d_step_fused(W3dPlan* plan, int s, double a, double b, double cscale, double ct,
+                   double* err_out, void* stream);
+int w3d_step_tma(W3dPlan* plan, int s, double a, double b, double cscale, double ct,
+                 const int32_t lo[3], const int32_t hi[3], double* err_out, int slot, void* stream);
+int w3d_step_box(W3dPlan* plan, int s, double a, double b, double cscale, double ct,
+                 const int32_t lo[3], const int32_t hi[3], double* err_out, int slot, void* stream);
+
+/* NCCL-baseline helpers (K5): contiguous face buffers of the unknowns of the two
+ * other axes, fastest index first.  ghost=0 packs/unpacks the edge layer of
+ * unknowns, ghost=1 the ghost layer. */
+int w3d_pack_face(W3dPlan* plan, int parity, int axis, int side, int ghost, double* buf, void* stream);
+int w3d_unpack_face(W3dPlan* plan, int parity, int axis, int side, int ghost, const double* buf, void* stream);
+/* periodic axis owned by one rank: copy edges into the opposite ghosts */
+int w3d_wrap_axis(W3dPlan* plan, int parity, int axis, void* stream);
+
+/* Stand-alone error norms of one field (K6): out[0] = max |u - sx*sy*sz*ct| over the
+ * unknowns, out[1] = sum of squares.  `workspace` is scratch of at least
+ * w3d_error_workspace_bytes() bytes; its first 4 bytes must be zero on first use
+ * (the kernel leaves them zero again). */
+size_t w3d_error_workspace_bytes(void);
+int w3d_error_norms(const double* u, const W3dBlock* blk, const double* sx, const double* sy,
+                    const double* sz, double ct, double* out, void* workspace,
+                    size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,212 @@
+"""ctypes binding of libwave3d_b200.so (include/wave3d.h) — the sm_100a kernels.
+
+The library is plain C ABI built in-tree by nvcc (no torch headers): Python hands
+it raw device pointers of torch tensors and the current CUDA stream handle, so
+every launch lands on torch's stream and can be captured in a CUDA graph.
+
+Reference parity: these are the kernels the reference's mpigpu-1.cu needed
+(report.pdf p.14-17 §4), re-designed for B200.
+There is deliberately NO eager/PyTorch fallback here: if the extension cannot be
+loaded on a GPU box the import fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from functools import lru_cache
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from ..build import CUDA_LIB, ensure
+from .cpu import W3dBlock
+
+XOFF = 15
+PITCH_ALIGN = 16
+ERR_SLOTS = 8
+
+
+class W3dPeer(C.Structure):
+    _fields_ = [("active", C.c_int32), ("ghost_index", C.c_int32), ("field", C.c_void_p * 2),
+                ("pitch", C.c_int64), ("plane", C.c_int64), ("flag", C.c_void_p), ("err_slot", C.c_void_p)]
+
+
+class W3dPlanDesc(C.Structure):
+    _fields_ = [("blk", W3dBlock), ("field", C.c_void_p * 2), ("tab", C.c_void_p * 3),
+                ("coef", C.c_double * 3), ("peer", W3dPeer * 6), ("flags_in", C.c_void_p),
+                ("status", C.c_void_p), ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+                ("variant", C.c_int32), ("zchunk", C.c_int32), ("num_sms", C.c_int32),
+                ("spin_timeout_ms", C.c_int32)]
+
+
+class CudaLibError(RuntimeError):
+    pass
+
+
+@lru_cache(maxsize=1)
+def lib() -> C.CDLL:
+    path = ensure(CUDA_LIB)
+    l = C.CDLL(str(path))
+    vp, i32p, dbl = C.c_void_p, C.POINTER(C.c_int32), C.c_double
+    l.w3d_last_error.restype = C.c_char_p
+    l.w3d_version.restype = C.c_char_p
+    l.w3d_workspace_bytes.restype = C.c_size_t
+    l.w3d_error_workspace_bytes.restype = C.c_size_t
+    l.w3d_pitch_for.restype = C.c_int64
+    l.w3d_pitch_for.argtypes = [C.c_int32]
+    l.w3d_plan_create.argtypes = [C.POINTER(W3dPlanDesc), C.POINTER(vp)]
+    l.w3d_plan_destroy.argtypes = [vp]
+    l.w3d_plan_destroy.restype = None
+    l.w3d_plan_describe.argtypes = [vp]
+    l.w3d_plan_describe.restype = C.c_char_p
+    l.w3d_plan_launches.argtypes = [vp]
+    l.w3d_plan_launches.restype = C.c_longlong
+    l.w3d_plan_init.argtypes = [vp, vp]
+    l.w3d_plan_set_ct_table.argtypes = [vp, vp]
+    l.w3d_step_fused.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
+    l.w3d_step_tma.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, i32p, i32p, vp, C.c_int, vp]
+    l.w3d_step_box.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, i32p, i32p, vp, C.c_int, vp]
+    l.w3d_pack_face.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
+    l.w3d_unpack_face.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
+    l.w3d_wrap_axis.argtypes = [vp, C.c_int, C.c_int, vp]
+    l.w3d_error_norms.argtypes = [vp, C.POINTER(W3dBlock), vp, vp, vp, dbl, vp, vp, C.c_size_t, vp]
+    return l
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise CudaLibError(f"libwave3d_b200 error {rc}: {lib().w3d_last_error().decode()}")
+
+
+def pitch_for(nx: int) -> int:
+    need = XOFF + nx + 2
+    return (need + PITCH_ALIGN - 1) // PITCH_ALIGN * PITCH_ALIGN
+
+
+def make_block(n: Sequence[int]) -> W3dBlock:
+    b = W3dBlock()
+    b.n[:] = list(n)
+    b.xoff = XOFF
+    b.pitch = pitch_for(n[0])
+    return b
+
+
+def field_shape(n: Sequence[int]) -> Tuple[int, int, int]:
+    return (n[2] + 2, n[1] + 2, pitch_for(n[0]))
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def workspace_bytes() -> int:
+    return int(lib().w3d_workspace_bytes())
+
+
+def _box(v: Optional[Sequence[int]]):
+    return None if v is None else (C.c_int32 * 3)(*v)
+
+
+class PeerSpec:
+    """Where one of my faces has to be delivered (all integers are device addresses)."""
+
+    def __init__(self, field_ptrs: Sequence[int], ghost_index: int, pitch: int, plane: int, flag_ptr: int):
+        self.field_ptrs = tuple(field_ptrs)
+        self.ghost_index = ghost_index
+        self.pitch = pitch
+        self.plane = plane
+        self.flag_ptr = flag_ptr
+
+
+class CudaPlan:
+    """Owns a W3dPlan handle plus the torch tensors it points into."""
+
+    def __init__(self, n: Sequence[int], fields: Sequence[torch.Tensor], tables: Sequence[torch.Tensor],
+                 coef: Sequence[float], flags_in: torch.Tensor, status: torch.Tensor,
+                 workspace: torch.Tensor, peers: Optional[dict] = None, variant: int = -1,
+                 zchunk: int = 0, spin_timeout_ms: int = 0):
+        self.n = tuple(int(x) for x in n)
+        self.blk = make_block(self.n)
+        self.fields = list(fields)
+        self.tables = list(tables)
+        self.flags_in, self.status, self.workspace = flags_in, status, workspace
+        shape = field_shape(self.n)
+        for f in self.fields:
+            assert f.is_cuda and f.dtype == torch.float64 and tuple(f.shape) == shape and f.is_contiguous()
+        for t, nn in zip(self.tables, self.n):
+            assert t.is_cuda and t.dtype == torch.float64 and t.numel() == nn + 2
+        d = W3dPlanDesc()
+        d.blk = self.blk
+        d.field[0], d.field[1] = self.fields[0].data_ptr(), self.fields[1].data_ptr()
+        for k in range(3):
+            d.tab[k] = self.tables[k].data_ptr()
+            d.coef[k] = float(coef[k])
+        for f, spec in (peers or {}).items():
+            pr = d.peer[f]
+            pr.active = 1
+            pr.ghost_index = spec.ghost_index
+            pr.field[0], pr.field[1] = spec.field_ptrs
+            pr.pitch, pr.plane = spec.pitch, spec.plane
+            pr.flag = spec.flag_ptr
+        d.flags_in = flags_in.data_ptr()
+        d.status = status.data_ptr()
+        d.workspace = workspace.data_ptr()
+        d.workspace_bytes = workspace.numel() * workspace.element_size()
+        d.variant, d.zchunk, d.num_sms, d.spin_timeout_ms = variant, zchunk, 0, spin_timeout_ms
+        self._desc = d
+        h = C.c_void_p()
+        check(lib().w3d_plan_create(C.byref(d), C.byref(h)))
+        self._h = h
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            lib().w3d_plan_destroy(h)
+            self._h = None
+
+    def describe(self) -> str:
+        return lib().w3d_plan_describe(self._h).decode()
+
+    @property
+    def launches(self) -> int:
+        return int(lib().w3d_plan_launches(self._h))
+
+    def init(self) -> None:
+        check(lib().w3d_plan_init(self._h, stream_ptr()))
+
+    def set_ct_table(self, table: Optional[torch.Tensor]) -> None:
+        self._ct_table = table
+        check(lib().w3d_plan_set_ct_table(self._h, None if table is None else table.data_ptr()))
+
+    @staticmethod
+    def _err_ptr(err_out: Optional[torch.Tensor]):
+        return None if err_out is None else err_out.data_ptr()
+
+    def step_fused(self, s: int, a: float, b: float, cscale: float, ct: float,
+                   err_out: Optional[torch.Tensor] = None) -> None:
+        check(lib().w3d_step_fused(self._h, s, a, b, cscale, ct, self._err_ptr(err_out), stream_ptr()))
+
+    def step_tma(self, s, a, b, cscale, ct, lo=None, hi=None, err_out=None, slot=0) -> None:
+        check(lib().w3d_step_tma(self._h, s, a, b, cscale, ct, _box(lo), _box(hi), self._err_ptr(err_out),
+                                 slot, stream_ptr()))
+
+    def step_box(self, s, a, b, cscale, ct, lo=None, hi=None, err_out=None, slot=0) -> None:
+        check(lib().w3d_step_box(self._h, s, a, b, cscale, ct, _box(lo), _box(hi), self._err_ptr(err_out),
+                                 slot, stream_ptr()))
+
+    def pack_face(self, parity: int, axis: int, side: int, buf: torch.Tensor, ghost: bool = False) -> None:
+        check(lib().w3d_pack_face(self._h, parity, axis, side, int(ghost), buf.data_ptr(), stream_ptr()))
+
+    def unpack_face(self, parity: int, axis: int, side: int, buf: torch.Tensor, ghost: bool = True) -> None:
+        check(lib().w3d_unpack_face(self._h, parity, axis, side, int(ghost), buf.data_ptr(), stream_ptr()))
+
+    def wrap_axis(self, parity: int, axis: int) -> None:
+        check(lib().w3d_wrap_axis(self._h, parity, axis, stream_ptr()))
+
+
+def error_norms(u: torch.Tensor, n: Sequence[int], tables: Sequence[torch.Tensor], ct: float,
+                out: torch.Tensor, workspace: torch.Tensor) -> None:
+    """Stand-alone error reduction (K6): out[0] = max error, out[1] = sum of squares."""
+    blk = make_block(n)
+    check(lib().w3d_error_norms(u.data_ptr(), C.byref(blk), tables[0].data_ptr(), tables[1].data_ptr(),
+                                tables[2].data_ptr(), ct, out.data_ptr(), workspace.data_ptr(),
+                                workspace.numel() * workspace.element_size(), stream_ptr()))

@@ -1,0 +1,262 @@
+"""Fused multi-GPU solver: one kernel per time step, halo exchange inside it.
+
+This is the product path (BASELINE.json north star).  Where the reference's
+MPI+CUDA program staged halos D2H -> MPI_Sendrecv -> H2D every step (separate
+"H2D/D2H" and "MPI" columns in report.pdf p.16 §4.4) and reduced the error with
+MPI, here:
+
+  * every rank's two field arrays and its flag words live in symmetric memory
+    (``torch.distributed._symmetric_memory``), so a kernel on GPU A can store to
+    GPU B's arrays over NVLink 5 / NVSwitch;
+  * ``w3d_step_fused`` computes the shell first, stores it locally and into the
+    neighbours' ghost layers, and releases a system-scope flag; the neighbours'
+    shell CTAs acquire that flag before their next step — no host, no NCCL;
+  * the error max / sum-of-squares is an epilogue of the same kernel; the only
+    collective left is one tiny all-gather of the per-step scalars *after* the
+    time loop.
+
+With world size 1 the same code runs on plain device tensors (a periodic axis
+wraps onto the rank itself through the same peer mechanism).
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ..models.analytic import time_table
+from ..models.problem import WaveProblem
+from ..ops import cuda
+from ..utils.report import RunResult
+from .decomp import RankBlock, local_tables, plan_all, plan_rank
+from .exchange import step_coeffs
+
+_FLAG_BYTES = 256     # 6 flag words + padding, at the head of the symmetric buffer
+
+
+def _field_bytes(n: Sequence[int]) -> int:
+    a, b, c = cuda.field_shape(n)
+    return a * b * c * 8
+
+
+class FusedSolver:
+    def __init__(self, p: WaveProblem, dims: Sequence[int] = (1, 1, 1), device: Optional[torch.device] = None,
+                 group=None, every: int = 2, variant: int = -1, zchunk: int = 0, use_graph: bool = True,
+                 spin_timeout_ms: int = 0):
+        self.p, self.dims, self.every = p, tuple(int(d) for d in dims), every
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        if self.world != self.dims[0] * self.dims[1] * self.dims[2]:
+            raise ValueError(f"dims {self.dims} do not match world size {self.world}")
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.use_graph = use_graph
+        blocks = plan_all(p, self.dims)
+        self.blk = blocks[self.rank]
+        blk = self.blk
+        fbytes = max(_field_bytes(b.n) for b in blocks)
+        fbytes = (fbytes + 255) // 256 * 256
+        total = _FLAG_BYTES + 2 * fbytes
+        # ---- storage: symmetric when there are real peers ----
+        self.symm = None
+        if self.world > 1:
+            import torch.distributed._symmetric_memory as symm_mem
+            buf = symm_mem.empty(total, dtype=torch.uint8, device=self.device)
+            self.symm = symm_mem.rendezvous(buf, group if group is not None else dist.group.WORLD)
+            base_ptrs = [int(x) for x in self.symm.buffer_ptrs]
+        else:
+            buf = torch.empty(total, dtype=torch.uint8, device=self.device)
+            base_ptrs = [buf.data_ptr()]
+        buf.zero_()
+        self.buf = buf
+        shape = cuda.field_shape(blk.n)
+        nel = shape[0] * shape[1] * shape[2]
+        self.flags = buf[:_FLAG_BYTES].view(torch.int64)
+        self.f = [buf[_FLAG_BYTES + q * fbytes: _FLAG_BYTES + q * fbytes + nel * 8].view(torch.float64).view(shape)
+                  for q in range(2)]
+        self.tab = [torch.from_numpy(t).to(self.device) for t in local_tables(p, blk)]
+        self.status = torch.zeros(4, dtype=torch.int32, device=self.device)
+        self.ws = torch.zeros(cuda.workspace_bytes(), dtype=torch.uint8, device=self.device)
+        self.trace = torch.zeros((p.K + 1, 2), dtype=torch.float64, device=self.device)
+        # ---- peers ----
+        peers: Dict[int, cuda.PeerSpec] = {}
+        for d in range(3):
+            for s in range(2):
+                r = blk.nbr[d][s]
+                if r < 0:
+                    continue
+                pb = blocks[r]
+                pshape = cuda.field_shape(pb.n)
+                # my low edge fills the peer's HIGH ghost (index n+1), my high edge its LOW ghost (0)
+                ghost = pb.n[d] + 1 if s == 0 else 0
+                base = base_ptrs[r] if self.world > 1 else base_ptrs[0]
+                peers[d * 2 + s] = cuda.PeerSpec(
+                    field_ptrs=(base + _FLAG_BYTES, base + _FLAG_BYTES + fbytes), ghost_index=ghost,
+                    pitch=pshape[2], plane=pshape[1] * pshape[2],
+                    flag_ptr=base + 8 * (d * 2 + (1 - s)))
+        self.plan = cuda.CudaPlan(blk.n, self.f, self.tab, p.coeffs(), self.flags, self.status, self.ws,
+                                  peers=peers, variant=variant, zchunk=zchunk, spin_timeout_ms=spin_timeout_ms)
+        self.ct = time_table(p)
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.kernel_launches = 0
+
+    # ------------------------------------------------------------------
+    def describe(self) -> str:
+        return self.plan.describe()
+
+    def barrier(self) -> None:
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            dist.barrier(self.group)
+
+    def init(self) -> None:
+        """Layer 0 everywhere (ghosts included), zero second array, flags reset.
+
+        All ranks must have finished this before any rank's first step may push
+        into their ghosts, hence the barrier."""
+        self.plan.init()
+        self.trace.zero_()
+        self.barrier()
+
+    def step(self, n: int, want_err: bool = True) -> None:
+        """Produce time level n (n = 1 is the Taylor step)."""
+        a, b, cs = step_coeffs(n)
+        self.plan.step_fused(n - 1, a, b, cs, float(self.ct[n]), self.trace[n] if want_err else None)
+        self.kernel_launches += 1
+
+    def _enqueue_steps(self, first: int, last: int) -> None:
+        for n in range(first, last + 1):
+            self.step(n, n % self.every == 0)
+
+    def capture(self) -> None:
+        """Capture steps 1..K into one CUDA graph (launch-bound at small blocks)."""
+        if self.graph is not None:
+            return
+        # warm the kernels once outside capture (lazy module load is not capturable)
+        self.init()
+        self._enqueue_steps(1, min(2, self.p.K))
+        self.barrier()
+        g = torch.cuda.CUDAGraph()
+        self.init()
+        with torch.cuda.graph(g):
+            self._enqueue_steps(1, self.p.K)
+        self.graph = g
+        self.barrier()
+
+    def run_steps(self) -> None:
+        """Enqueue all K steps on the current stream (graph replay if captured)."""
+        if self.use_graph and self.graph is not None:
+            self.graph.replay()
+            self.kernel_launches += self.p.K
+        else:
+            self._enqueue_steps(1, self.p.K)
+
+    def check_status(self) -> None:
+        st = int(self.status[0].item())
+        if st != 0:
+            raise RuntimeError(f"rank {self.rank}: device watchdog tripped (status 0x{st:x}): "
+                               "a neighbour's halo flag never arrived")
+
+    def gather_trace(self) -> List[Tuple[int, float, float, float]]:
+        """Combine the per-rank (max, sum sq) rows: one all-gather after the loop."""
+        t = self.trace
+        if self.world > 1:
+            allt = [torch.empty_like(t) for _ in range(self.world)]
+            dist.all_gather(allt, t, group=self.group)
+            st = torch.stack(allt)                       # (world, K+1, 2)
+            mx = st[:, :, 0].max(dim=0).values
+            s2 = st[:, :, 1].cpu().double()
+            s2 = sum(s2[r] for r in range(self.world))   # fixed rank order
+            mx = mx.cpu()
+        else:
+            tc = t.cpu()
+            mx, s2 = tc[:, 0], tc[:, 1]
+        p = self.p
+        return [(n, n * p.tau, float(mx[n]), math.sqrt(float(s2[n]) / p.n_unknowns))
+                for n in range(1, p.K + 1) if n % self.every == 0]
+
+    def run(self, verbose: bool = False) -> RunResult:
+        """Whole run with device timing (CUDA events, max over ranks)."""
+        p = self.p
+        if self.use_graph and self.graph is None:
+            self.capture()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        self.barrier()
+        ev[0].record()
+        self.plan.init()
+        self.trace.zero_()
+        self.barrier()          # flags must be reset everywhere before anyone pushes
+        ev[1].record()
+        self.run_steps()
+        ev[2].record()
+        self.barrier()
+        self.check_status()
+        t_init = ev[0].elapsed_time(ev[1]) / 1e3
+        t_loop = ev[1].elapsed_time(ev[2]) / 1e3
+        tt = torch.tensor([t_init, t_loop], dtype=torch.float64, device=self.device)
+        if self.world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX, group=self.group)
+        t_init, t_loop = (float(v) for v in tt.cpu())
+        trace = self.gather_trace()
+        res = RunResult(backend="fused", N=p.N, L=p.L, tau=p.tau, K=p.K, bc=p.bc, world_size=self.world,
+                        decomp=self.dims, trace=trace, updates=p.updates,
+                        phases={"total": t_init + t_loop, "init": t_init, "compute": t_loop, "loop": t_loop,
+                                "h2d_d2h": 0.0, "exchange": 0.0},
+                        extra={"plan": self.describe(), "graph": bool(self.use_graph)})
+        if verbose and self.rank == 0:
+            for line in res.lines(self.every):
+                print(line)
+        return res
+
+    def field(self, parity: int) -> torch.Tensor:
+        xo = cuda.XOFF + 1
+        return self.f[parity][1:-1, 1:-1, xo: xo + self.blk.n[0]].contiguous()
+
+
+class StreamingSession:
+    """Step-by-step public API: the host feeds each step and reads each step's result.
+
+    ``session.step(n)`` (1) copies that step's time factor cos(a_t t_n) from pinned
+    host memory to the device table the kernel reads, (2) launches the fused step,
+    (3) copies the step's (max error, sum of squares) back to pinned host memory and
+    waits for it.  This is the end-to-end path a user drives when they want the error
+    of every step as it happens, the way the reference prints its ``Step`` lines while
+    running (report.pdf p.15-16); ``bench.py`` times it as the ``e2e`` number.
+    """
+
+    H2D_BYTES_PER_STEP = 8
+    D2H_BYTES_PER_STEP = 16
+
+    def __init__(self, solver: FusedSolver):
+        self.s = solver
+        p = solver.p
+        self.ct_host = torch.from_numpy(solver.ct.copy()).pin_memory()
+        self.ct_dev = torch.zeros(p.K + 2, dtype=torch.float64, device=solver.device)
+        self.err_host = torch.zeros((p.K + 1, 2), dtype=torch.float64).pin_memory()
+        solver.plan.set_ct_table(self.ct_dev)
+
+    def close(self) -> None:
+        self.s.plan.set_ct_table(None)
+
+    def start(self) -> None:
+        """Upload the analytic tables from pinned host memory and build layer 0."""
+        s = self.s
+        from .decomp import local_tables
+        self.tab_host = [torch.from_numpy(t).pin_memory() for t in local_tables(s.p, s.blk)]
+        for dst, src in zip(s.tab, self.tab_host):
+            dst.copy_(src, non_blocking=True)
+        s.init()
+
+    @property
+    def table_bytes(self) -> int:
+        return sum(t.numel() * 8 for t in self.s.tab)
+
+    def step(self, n: int) -> Tuple[float, float]:
+        s = self.s
+        self.ct_dev[n: n + 1].copy_(self.ct_host[n: n + 1], non_blocking=True)
+        s.step(n, True)
+        self.err_host[n].copy_(s.trace[n], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(self.err_host[n, 0]), float(self.err_host[n, 1])

@@ -1,0 +1,210 @@
+"""sm_100a kernels vs the native CPU solver (bit-exact) and the plain-PyTorch
+restatement (tolerance).  Needs a B200: run under gpurun with ``-m gpu``.
+
+Reference parity: "error of MPI+GPU fully matches the sequential version"
+(report.pdf p.16 §4.3) and the published 512^3 trace (p.15-16).
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from mpi_cuda_b200 import WaveProblem
+from mpi_cuda_b200.models import analytic, wave_torch
+from mpi_cuda_b200.ops import cpu
+from mpi_cuda_b200.parallel.decomp import local_tables, plan_rank
+from mpi_cuda_b200.utils import report
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _cuda_ops(p, variant=-1, zchunk=0, kernel="tma"):
+    from mpi_cuda_b200.parallel.exchange import CudaBlockOps
+    blk = plan_rank(p, (1, 1, 1), 0)
+    return CudaBlockOps(p, blk, _dev(), variant=variant, zchunk=zchunk, kernel=kernel), blk
+
+
+def _cpu_fields(p, steps):
+    """Native CPU run on the same (unpadded) block; returns list of fields per level."""
+    blk = plan_rank(p, (1, 1, 1), 0)
+    b = cpu.make_block(blk.n)
+    tab = local_tables(p, blk)
+    A = np.zeros(cpu.block_shape(b)); B = np.zeros_like(A)
+    cpu.init(A, b, *tab)
+    f = [A, B]
+    c = p.coeffs()
+    out = [A[1:-1, 1:-1, 1:-1].copy()]
+    for n in range(1, steps + 1):
+        s = n - 1
+        for d in range(3):
+            if p.periodic[d]:
+                cpu.wrap(f[s & 1], b, d)
+        a, bb, cs = (1.0, 0.0, 0.5) if n == 1 else (2.0, -1.0, 1.0)
+        cpu.step(f[(s & 1) ^ 1], f[s & 1], b, a, bb, [cs * v for v in c])
+        out.append(f[(s & 1) ^ 1][1:-1, 1:-1, 1:-1].copy())
+    return out, tab, b
+
+
+def test_library_loads_and_reports_version():
+    from mpi_cuda_b200.ops import cuda
+    assert b"sm_100a" in cuda.lib().w3d_version()
+    assert torch.cuda.get_device_capability(0)[0] == 10
+
+
+def test_init_kernel_matches_tables():
+    p = WaveProblem((37, 21, 18), 1.0, 1e-3, 2)
+    ops, blk = _cuda_ops(p)
+    ops.init()
+    torch.cuda.synchronize()
+    sx, sy, sz = local_tables(p, blk)
+    want = sz[:, None, None] * sy[None, :, None] * sx[None, None, :]
+    from mpi_cuda_b200.ops.cuda import XOFF
+    got = ops.f[0].cpu().numpy()
+    assert np.array_equal(got[:, :, XOFF: XOFF + blk.n[0] + 2], sx[None, None, :] * (sy[None, :, None] * sz[:, None, None]))
+    assert np.allclose(got[:, :, XOFF: XOFF + blk.n[0] + 2], want, rtol=0, atol=1e-15)
+    assert np.count_nonzero(got[:, :, :XOFF]) == 0
+    assert float(ops.f[1].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("kernel,variant", [("box", -1), ("tma", 0), ("tma", 1), ("tma", 2), ("tma", 3)])
+@pytest.mark.parametrize("N", [(33, 19, 11), (130, 37, 45), (257, 40, 23)])
+def test_step_kernels_bit_exact_vs_cpu(kernel, variant, N):
+    p = WaveProblem(N, 1.0, 1e-3, 5)
+    ops, blk = _cuda_ops(p, variant=variant, kernel=kernel)
+    ref, tab, b = _cpu_fields(p, p.K)
+    ops.init()
+    ct = analytic.time_table(p)
+    for n in range(1, p.K + 1):
+        a, bb, cs = (1.0, 0.0, 0.5) if n == 1 else (2.0, -1.0, 1.0)
+        ops.step(n - 1, a, bb, cs, float(ct[n]), True, n)
+        got = ops.field(n & 1).cpu().numpy()
+        assert np.array_equal(got, ref[n]), f"level {n}: max diff {np.max(np.abs(got - ref[n]))}"
+        mx, s2 = (float(v) for v in ops.local_error(n).cpu())
+        # epilogue vs CPU error of the same field
+        full = np.zeros(cpu.block_shape(b)); full[1:-1, 1:-1, 1:-1] = ref[n]
+        cmx, cs2 = cpu.error(full, b, *tab, float(ct[n]))
+        assert mx == cmx
+        assert abs(s2 - cs2) <= 1e-12 * cs2
+    assert int(ops.status[0]) == 0
+
+
+@pytest.mark.parametrize("zchunk", [1, 3, 7, 64])
+def test_tma_zchunk_seams(zchunk):
+    p = WaveProblem((140, 50, 30), 1.0, 1e-3, 3)
+    ops, _ = _cuda_ops(p, variant=0, zchunk=zchunk)
+    ref, _, _ = _cpu_fields(p, p.K)
+    ops.init()
+    ct = analytic.time_table(p)
+    for n in range(1, p.K + 1):
+        a, bb, cs = (1.0, 0.0, 0.5) if n == 1 else (2.0, -1.0, 1.0)
+        ops.step(n - 1, a, bb, cs, float(ct[n]), False, n)
+    assert np.array_equal(ops.field(p.K & 1).cpu().numpy(), ref[p.K])
+
+
+def test_step_vs_plain_pytorch_reference():
+    """Numerics against the whole-array PyTorch restatement of the same op."""
+    p = WaveProblem(48, 1.0, 1e-3, 6)
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
+    res = s.run()
+    ref_trace, ref_field = wave_torch.solve(p, every=1, return_field=True)
+    got = s.field(p.K & 1).cpu()
+    assert torch.max(torch.abs(got - ref_field[1:-1, 1:-1, 1:-1])) < 5e-15
+    for a, b in zip(res.trace, ref_trace):
+        assert abs(a[2] - b[2]) <= 5e-15 and abs(a[3] - b[3]) <= 1e-9 * b[3]
+
+
+def test_standalone_error_kernel_matches_epilogue():
+    from mpi_cuda_b200.ops import cuda
+    p = WaveProblem((70, 33, 29), 1.0, 1e-3, 3)
+    ops, blk = _cuda_ops(p, variant=1)
+    ops.init()
+    ct = analytic.time_table(p)
+    for n in range(1, 4):
+        a, bb, cs = (1.0, 0.0, 0.5) if n == 1 else (2.0, -1.0, 1.0)
+        ops.step(n - 1, a, bb, cs, float(ct[n]), True, n)
+    out = torch.zeros(2, dtype=torch.float64, device=_dev())
+    ws = torch.zeros(int(cuda.lib().w3d_error_workspace_bytes()), dtype=torch.uint8, device=_dev())
+    for _ in range(2):   # twice: the kernel must leave its ticket ready for reuse
+        cuda.error_norms(ops.f[3 & 1], blk.n, ops.tab, float(ct[3]), out, ws)
+        mx, s2 = (float(v) for v in out.cpu())
+        emx, es2 = (float(v) for v in ops.local_error(3).cpu())
+        assert mx == emx and abs(s2 - es2) <= 1e-12 * es2
+
+
+def test_pack_unpack_matches_cpu():
+    p = WaveProblem((21, 14, 9), 1.0, 1e-3, 1)
+    ops, blk = _cuda_ops(p)
+    g = torch.Generator().manual_seed(1)
+    host = torch.randn(ops.f[0].shape, dtype=torch.float64, generator=g)
+    ops.f[0].copy_(host)
+    from mpi_cuda_b200.ops.cuda import XOFF, pitch_for
+    b = cpu.make_block(blk.n, xoff=XOFF, pitch=pitch_for(blk.n[0]))
+    for axis in range(3):
+        for side in range(2):
+            buf = torch.empty(blk.face_elems(axis), dtype=torch.float64, device=_dev())
+            ops.plan.pack_face(0, axis, side, buf, ghost=False)
+            want = cpu.pack(host.numpy(), b, axis, side, ghost=False)
+            assert np.array_equal(buf.cpu().numpy(), want)
+            ops.plan.unpack_face(1, axis, side, buf, ghost=True)
+            chk = np.zeros(host.shape); cpu.unpack(chk, b, axis, side, want, ghost=True)
+            f1 = ops.f[1].cpu().numpy()
+            assert np.array_equal(f1 != 0, chk != 0) or np.array_equal(f1[chk != 0], chk[chk != 0])
+    assert True
+
+
+@pytest.mark.parametrize("bc", ["ddp", "ppp", "pdd"])
+def test_fused_periodic_self_wrap_matches_cpu(bc):
+    """Periodic axes on one GPU go through the same in-kernel peer-store + flag path."""
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem((40, 36, 28), 2.0, 1e-3, 8, bc=bc)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=False)
+    res = s.run()
+    base, _ = cpu.solve(p, every=2)
+    for a, b in zip(res.trace, base):
+        assert a[2] == b[2]
+        assert abs(a[3] - b[3]) <= 1e-12 * b[3]
+    ref, _, _ = _cpu_fields(p, p.K)
+    assert np.array_equal(s.field(p.K & 1).cpu().numpy(), ref[p.K])
+
+
+def test_fused_graph_replay_equals_eager():
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem(64, 1.0, 1e-3, 10)
+    a = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=False).run()
+    g = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=True)
+    r1 = g.run(); r2 = g.run()
+    assert a.trace == r1.trace == r2.trace
+    ora = analytic.oracle_trace(p, 2)
+    for x, o in zip(r1.trace, ora):
+        assert abs(x[2] - o[2]) <= 1e-13 + 1e-6 * o[2]
+
+
+def test_streaming_session_matches_batch():
+    from mpi_cuda_b200.parallel.fused import FusedSolver, StreamingSession
+    p = WaveProblem(56, 1.0, 1e-3, 6)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
+    batch = s.run().trace
+    sess = StreamingSession(s)
+    sess.start()
+    got = [sess.step(n) for n in range(1, p.K + 1)]
+    sess.close()
+    for (mx, s2), b in zip(got, batch):
+        assert mx == b[2] and abs(math.sqrt(s2 / p.n_unknowns) - b[3]) <= 1e-15 * b[3]
+
+
+def test_golden_trace_512_on_gpu():
+    """Published trace of the reference (report.pdf p.15-16 §4.3), on one B200."""
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem(512, 1.0, 1e-3, 20)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=True)
+    res = s.run()
+    assert len(res.trace) == 10
+    for (n, t, mx, l2), (gn, gt, gmx, gl2) in zip(res.trace, report.GOLDEN_512):
+        assert n == gn and abs(mx - gmx) <= 5e-15 and abs(l2 - gl2) <= 1e-6 * gl2
+    assert res.lines()[-1][:60] == "Step 20, t = 0.020000, Max Error = 3.960129e-09, L2 Error = 1.40422"[:60]

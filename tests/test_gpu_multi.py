@@ -1,0 +1,65 @@
+"""Multi-GPU: fused P2P path vs NCCL baseline vs 1 GPU (digit-level trace equality).
+
+Runs only where >= 2 GPUs are visible (``gpurun --gpus 2``).  One process per GPU.
+Reference parity: 1-GPU and 2-GPU traces identical (report.pdf p.15-16 §4.3).
+"""
+import pytest
+import torch
+
+from mpi_cuda_b200 import WaveProblem
+from mpi_cuda_b200.ops import cpu
+from mpi_cuda_b200.parallel.launch import spawn
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+
+def _work(rank, world, mode, dims, bc, N, K, graph):
+    import torch
+    from mpi_cuda_b200.parallel.exchange import CudaBlockOps, ExchangeSolver
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    dev = torch.device("cuda", rank)
+    p = WaveProblem(N, 2.0, 1e-3, K, bc=bc)
+    if mode == "fused":
+        s = FusedSolver(p, dims, dev, every=2, use_graph=graph, spin_timeout_ms=5000)
+        r = s.run()
+        r2 = s.run()
+        assert r.trace == r2.trace
+        return r.trace
+    s = ExchangeSolver(p, dims, lambda pp, b: CudaBlockOps(pp, b, dev), every=2, backend_name="nccl")
+    return s.run().trace
+
+
+def _ngpu():
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("mode", ["nccl", "fused"])
+@pytest.mark.parametrize("dims,bc", [((1, 1, 2), "ddd"), ((1, 2, 1), "ddp"), ((2, 1, 1), "ddd"), ((1, 1, 2), "ddp")])
+def test_two_gpu_trace_equals_one_gpu(mode, dims, bc):
+    N, K = (72, 60, 52), 8
+    base, _ = cpu.solve(WaveProblem(N, 2.0, 1e-3, K, bc=bc), every=2)
+    out = spawn(_work, 2, (mode, dims, bc, N, K, False), backend="nccl")
+    for trace in out:
+        assert [r[0] for r in trace] == [r[0] for r in base]
+        for a, b in zip(trace, base):
+            assert a[2] == b[2]
+            assert abs(a[3] - b[3]) <= 1e-12 * b[3]
+
+
+def test_two_gpu_fused_graph():
+    N, K = (96, 64, 64), 10
+    base, _ = cpu.solve(WaveProblem(N, 2.0, 1e-3, K), every=2)
+    out = spawn(_work, 2, ("fused", (1, 1, 2), "ddd", N, K, True), backend="nccl")
+    for a, b in zip(out[0], base):
+        assert a[2] == b[2]
+
+
+@pytest.mark.parametrize("dims", [(1, 2, 2), (2, 2, 1), (1, 1, 4)])
+def test_four_gpu_blocks(dims):
+    if _ngpu() < 4:
+        pytest.skip("needs 4 GPUs")
+    N, K = (80, 72, 64), 8
+    base, _ = cpu.solve(WaveProblem(N, 2.0, 1e-3, K, bc="dpd"), every=2)
+    out = spawn(_work, 4, ("fused", dims, "dpd", N, K, False), backend="nccl")
+    for a, b in zip(out[0], base):
+        assert a[2] == b[2]
