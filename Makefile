@@ -12,7 +12,7 @@ NVCCFLAGS := -ccbin $(CXX) $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false -Iinclud
 CU_SRCS   := $(wildcard csrc/cuda/*.cu)
 CU_HDRS   := $(wildcard csrc/cuda/*.cuh) $(wildcard include/*.h)
 
-all: cpu cuda
+all: cpu cuda tools
 
 cpu: $(OUT)/libwave3d_cpu.so $(BIN)/wave $(BIN)/openmpwave $(BIN)/mpi $(BIN)/mpiomp
 

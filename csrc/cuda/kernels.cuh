@@ -49,6 +49,7 @@ struct BoxTable {
 
 struct TileGeom {
   int lo[3], hi[3];   // box [lo,hi) in local unknown indices
+  int x0;             // x index of the first tile column (<= lo[0]; chosen so that TMA boxes start 16-B aligned)
   int ntx, nty, zc, nchunks;
 };
 
@@ -60,7 +61,7 @@ struct ErrCtl {
 };
 
 struct alignas(64) StepParams {
-  CUtensorMap map_halo;   // (TX+2)x(TY+2)x1 boxes of the current level
+  CUtensorMap map_halo;   // (TX+4)x(TY+2)x1 boxes of the current level
   CUtensorMap map_core;   // TX x TY x 1 boxes of the previous level (array updated in place)
   Geometry g;
   const double* cur;
@@ -238,7 +239,10 @@ template <int TX, int RPT, int RG, int STAGES>
 struct TileCfg {
   static constexpr int kTX = TX, kRPT = RPT, kRG = RG, kStages = STAGES;
   static constexpr int kTY = RPT * RG;
-  static constexpr int kW = TX + 2;
+  // The innermost TMA coordinate must be a multiple of 16 bytes (2 doubles) — an odd
+  // start faults with 'illegal instruction' on sm_100 (measured) — so the
+  // halo box carries two ghost columns on each side instead of one.
+  static constexpr int kW = TX + 4;
   static constexpr int kHaloRows = kTY + 2;
   static constexpr int kConsumers = TX * RG;
   static constexpr int kThreads = kConsumers + 32;
@@ -248,7 +252,7 @@ struct TileCfg {
   static constexpr int kStageBytes = kHaloBytesPad + kCoreBytes;
   static constexpr int kBarBytes = 128 + 1024;   // barriers + reduction scratch
   static constexpr int kSmemBytes = kBarBytes + STAGES * kStageBytes + 128;
-  static_assert(TX % 32 == 0 && TX <= 254, "TX must be a warp multiple and fit a TMA box");
+  static_assert(TX % 32 == 0 && TX <= 252, "TX must be a warp multiple and fit a TMA box");
   static_assert(kHaloRows <= 256, "TMA box limit");
   static_assert(2 * STAGES * 8 <= 128, "barrier area");
 };
@@ -264,7 +268,7 @@ __device__ void tma_role(const StepParams& P, int work, uint8_t* smem, double& m
   const int tx = work % T.ntx;
   const int ty = (work / T.ntx) % T.nty;
   const int ch = work / (T.ntx * T.nty);
-  const int x0 = T.lo[0] + tx * TX;
+  const int x0 = T.x0 + tx * TX;
   const int y0 = T.lo[1] + ty * Cfg::kTY;
   const int z0 = T.lo[2] + ch * T.zc;
   const int z1 = min(z0 + T.zc, T.hi[2]);
@@ -283,10 +287,16 @@ __device__ void tma_role(const StepParams& P, int work, uint8_t* smem, double& m
   const int warp = threadIdx.x >> 5;
   if (warp == Cfg::kConsumers / 32) {
     // ===== producer warp: one lane drives TMA =====
-    if ((threadIdx.x & 31) == 0) {
+    // The whole warp walks the loop (only lane 0 issues) so that it reaches the
+    // CTA-wide barrier after this role converged: an aligned bar.sync executed by
+    // a diverged warp faults on sm_100.
+    const bool leader = (threadIdx.x & 31) == 0;
+    if (leader) {
       tma_prefetch_desc(&P.map_halo);
       tma_prefetch_desc(&P.map_core);
-      for (int t = 0; t < iters; ++t) {
+    }
+    for (int t = 0; t < iters; ++t) {
+      if (leader) {
         const int s = t % STAGES;
         const uint32_t ph = (uint32_t)(t / STAGES) & 1u;
         mbar_wait(empty + s, ph ^ 1u);
@@ -294,18 +304,19 @@ __device__ void tma_role(const StepParams& P, int work, uint8_t* smem, double& m
         uint8_t* st = stage0 + (size_t)s * Cfg::kStageBytes;
         mbar_arrive_expect_tx(full + s, (uint32_t)(Cfg::kHaloBytes + (need_prev ? Cfg::kCoreBytes : 0)));
         const int zz = z0 - 1 + t;
-        tma_load_3d(st, &P.map_halo, full + s, P.g.xoff + x0 - 1, y0 - 1, zz);
+        tma_load_3d(st, &P.map_halo, full + s, P.g.xoff + x0 - 2, y0 - 1, zz);
         if (need_prev) tma_load_3d(st + Cfg::kHaloBytesPad, &P.map_core, full + s, P.g.xoff + x0, y0, zz);
       }
+      __syncwarp();
     }
-    return;   // callers re-converge all warps with __syncthreads() after this role
+    return;
   }
 
   // ===== consumers =====
   const int cxi = threadIdx.x % TX;           // column inside the tile
   const int r0 = (threadIdx.x / TX) * RPT;    // first row of this thread
   const int gx = x0 + cxi;                    // local x index
-  const bool x_ok = gx < T.hi[0];
+  const bool x_ok = gx >= T.lo[0] && gx < T.hi[0];
   const bool want_err = P.err.out != nullptr;
   const double ct = P.ct_ptr ? __ldg(P.ct_ptr) : P.ct;
   double acc[RPT], zm[RPT], sxy[RPT];
@@ -329,7 +340,7 @@ __device__ void tma_role(const StepParams& P, int work, uint8_t* smem, double& m
     const double* ps = reinterpret_cast<const double*>(stage0 + (size_t)s * Cfg::kStageBytes + Cfg::kHaloBytesPad);
     double col[RPT + 2];
 #pragma unroll
-    for (int q = 0; q < RPT + 2; ++q) col[q] = cs[(r0 + q) * W + cxi + 1];
+    for (int q = 0; q < RPT + 2; ++q) col[q] = cs[(r0 + q) * W + cxi + 2];
 
     if (t >= 2) {
       // plane zo = z0 + t - 2 is complete: add the z+1 neighbour, store, fold the error
@@ -352,8 +363,8 @@ __device__ void tma_role(const StepParams& P, int work, uint8_t* smem, double& m
     if (t >= 1 && t <= nzc) {
 #pragma unroll
       for (int r = 0; r < RPT; ++r) {
-        const double xm = cs[(r0 + r + 1) * W + cxi];
-        const double xp = cs[(r0 + r + 1) * W + cxi + 2];
+        const double xm = cs[(r0 + r + 1) * W + cxi + 1];
+        const double xp = cs[(r0 + r + 1) * W + cxi + 3];
         const double pv = ps[(r0 + r) * TX + cxi];
         acc[r] = w3d_partial(col[r + 1], pv, xm, xp, col[r], col[r + 2], zm[r], P.a, P.b, P.cx, P.cy, P.cz);
       }

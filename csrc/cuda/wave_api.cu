@@ -52,7 +52,7 @@ const Variant kVariants[] = {
     {Cfg3::kTX, Cfg3::kTY, Cfg3::kThreads, Cfg3::kSmemBytes, 1, fused_step_kernel<Cfg3, 1>, "64x32x4st"},
 };
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
-constexpr int kDefaultVariant = 1;
+constexpr int kDefaultVariant = 3;   // best of the measured sweep at 512^3 (profiles/variant_sweep.md)
 
 // ---- workspace layout ---------------------------------------------------------------
 constexpr size_t kCounterBytes = 256;   // tickets [0..7] at 0, shell counter at +64
@@ -115,7 +115,7 @@ int encode_maps(W3dPlan* p) {
   const cuuint64_t strides[2] = {(cuuint64_t)p->g.pitch * 8, (cuuint64_t)p->g.plane * 8};
   const cuuint32_t estr[3] = {1, 1, 1};
   for (int f = 0; f < 2; ++f) {
-    const cuuint32_t hb[3] = {(cuuint32_t)(v.tx + 2), (cuuint32_t)(v.ty + 2), 1};
+    const cuuint32_t hb[3] = {(cuuint32_t)(v.tx + 4), (cuuint32_t)(v.ty + 2), 1};
     const cuuint32_t cb[3] = {(cuuint32_t)v.tx, (cuuint32_t)v.ty, 1};
     CUresult r = enc(&p->halo[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, p->d.field[f], dims, strides, hb, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -135,7 +135,9 @@ void plan_tiles(const W3dPlan* p, const int lo[3], const int hi[3], int zchunk, 
   const Variant& v = kVariants[p->variant];
   for (int d = 0; d < 3; ++d) { t->lo[d] = lo[d]; t->hi[d] = hi[d]; }
   const int ex = std::max(0, hi[0] - lo[0]), ey = std::max(0, hi[1] - lo[1]), ez = std::max(0, hi[2] - lo[2]);
-  t->ntx = (ex + v.tx - 1) / v.tx;
+  // TMA boxes must start on an even element: shift the tile origin left by one if needed
+  t->x0 = lo[0] - ((p->g.xoff + lo[0]) & 1);
+  t->ntx = (hi[0] - t->x0 + v.tx - 1) / v.tx;
   t->nty = (ey + v.ty - 1) / v.ty;
   if (ex == 0 || ey == 0 || ez == 0) { t->ntx = t->nty = 0; t->zc = 1; t->nchunks = 0; return; }
   const long long tiles = (long long)t->ntx * t->nty;
