@@ -128,6 +128,26 @@ int w3d_error_norms(const double* u, const W3dBlock* blk, const double* sx, cons
                     const double* sz, double ct, double* out, void* workspace,
                     size_t workspace_bytes, void* stream);
 
+/* Same norms for callers that cannot allocate device memory (no counterpart in the
+ * reference: it is an addition of this library).  Meant for code that lives inside a
+ * host application with its own fixed memory pool, or inside someone else's time loop
+ * where a cudaMalloc would stall the whole device: such callers can supply inputs and
+ * the 2-double output, but no workspace.  The scratch is a static array inside the
+ * library instead — W3D_NOALLOC_SCRATCH_BYTES per GPU, held until the process exits —
+ * which limits the block to ny*nz <= W3D_NOALLOC_MAX_ROWS (nx is not limited); a larger
+ * block returns W3D_ETOOBIG and leaves `out` untouched.  No cudaMalloc/cudaFree or other
+ * allocating call is made.  The first call on a device resolves the array's address and
+ * should happen outside stream capture.  All calls on a device share the array: calls
+ * ordered on one stream are fine, calls that may overlap on the GPU race.  On failure
+ * the reason is written to errbuf (may be NULL).  out[0] = max error, out[1] = sum of
+ * squares, as for w3d_error_norms (the sum may differ in the last bits: other order). */
+#define W3D_ETOOBIG (-5)
+#define W3D_NOALLOC_MAX_ROWS 262144
+#define W3D_NOALLOC_SCRATCH_BYTES 33024
+int w3d_error_norms_noalloc(const double* u, const W3dBlock* blk, const double* sx, const double* sy,
+                            const double* sz, double ct, double* out, void* stream, char* errbuf,
+                            size_t errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif
