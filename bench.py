@@ -102,8 +102,8 @@ def main() -> int:
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
-    ap.add_argument("--N", type=int, default=512)
-    ap.add_argument("--L", type=float, default=1.0)
+    ap.add_argument("--N", default="512", help="intervals: one value or NxxNyxNz")
+    ap.add_argument("--L", default="1.0", help="box size: one value or LxxLyxLz; 'pi' multiples accepted (e.g. pi, 0.5pi)")
     ap.add_argument("--tau", type=float, default=1e-3)
     ap.add_argument("--bc", default="ddd")
     ap.add_argument("--backend", default="fused", choices=("fused", "nccl"))
@@ -133,7 +133,11 @@ def main() -> int:
         if rank == 0:
             print(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}; using {world}", file=sys.stderr)
     K, W = args.steps, max(args.warmup, 3)
-    p = WaveProblem(args.N, args.L, args.tau, K, bc=args.bc)
+    from mpi_cuda_b200.utils.cli import _num
+    Ns = [int(v) for v in str(args.N).lower().split("x")]
+    Ls = [_num(v) for v in str(args.L).lower().split("x")]
+    p = WaveProblem(Ns if len(Ns) == 3 else Ns[0], Ls if len(Ls) == 3 else Ls[0], args.tau, K, bc=args.bc)
+    grid_name = "%dx%dx%d" % p.N if len(set(p.N)) > 1 else "%d^3" % p.N[0]
     p.check_cfl()
     dims = parse_dims(args.decomp, world)
 
@@ -235,16 +239,17 @@ def main() -> int:
     halo_bytes = max(b.halo_bytes_per_step() for b in blocks)
     t_roof_ms = max(bytes_per_gpu / (hbm * 1e9), halo_bytes / 770e9) * 1e3
     out = {
-        "metric": "GLUP/s at %d^3 grid, K=%d steps, fp64, device-timed max over ranks (wall_s = total)" % (args.N, K),
+        "metric": "GLUP/s at %s grid, K=%d steps, fp64, device-timed max over ranks (wall_s = total)" % (grid_name, K),
         "value": glups, "unit": "GLUP/s", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": t_ms / K, "wall_s": t_ms / 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": glups / pub, "dtype": "fp64", "data": "synthetic (analytic-solution initial layers)",
-        "config": {"model": "wave3d leapfrog 7-point", "grid": f"{args.N}^3", "global_batch": p.n_unknowns,
+        "config": {"model": "wave3d leapfrog 7-point", "grid": grid_name, "global_batch": p.n_unknowns,
                    "seq_len": K, "parallelism": f"spatial {dims[0]}x{dims[1]}x{dims[2]}", "backend": args.backend,
-                   "bc": args.bc, "L": args.L, "tau": args.tau, "report_every": args.every,
+                   "bc": args.bc, "L": list(p.L), "tau": args.tau, "report_every": args.every,
                    "l2_policy": "inputs larger than L2 (2 x %.2f GB fields per GPU vs 126 MB L2), no flush"
                                 % (bytes_per_gpu / 24 * 8 / 1e9),
-                   "reps": args.reps, "rep_ms": [round(t, 4) for t in times], "cuda_graph": not args.no_graph,
+                   "reps": args.reps, "rep_ms": [round(t, 4) for t in times],
+                   "cuda_graph": (not args.no_graph) and args.backend == "fused",
                    "published_baseline": {"glups": pub, "wall_s": PUBLISHED_WALL_S.get(world, 0.505),
                                           "hardware": "%d x P100" % min(world, 2)}},
         "roofline": {"hbm_gbs_measured": hbm, "bytes_per_gpu_per_step": bytes_per_gpu,

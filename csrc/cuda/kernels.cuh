@@ -5,18 +5,22 @@
 // B200.  No reference source exists (readme.md:68 names the file only), so none
 // of this is derived from reference code.
 //
-//  * `tma_role`   — z-marching stencil: one producer lane streams (TX+2)x(TY+2)
+//  * `tma_role`   — z-marching stencil: one producer lane streams (TX+4)x(TY+2)
 //                   planes of u^n and TXxTY planes of u^{n-1} into a shared-memory
 //                   ring with cp.async.bulk.tensor (TMA) + mbarriers; consumer
 //                   warps keep the z-direction in registers, update in place and
 //                   fold max|err| / sum err^2 into the epilogue.
-//  * `shell_role` — nodes adjacent to a neighbour: acquire the neighbours' flags,
-//                   compute, store locally AND into the neighbours' ghost layers
-//                   over NVLink (plain st.global on peer-mapped addresses); the
-//                   last shell CTA releases the flags for the next level.
-//  * `fused_step_kernel` — both roles in ONE launch: low block indices are shell
-//                   CTAs (scheduled first), the rest stream the interior while the
-//                   P2P stores are in flight.
+//  * fused halo exchange — CTAs whose tile touches a face that has a neighbour
+//                   ("face CTAs") are numbered first, so the hardware dispatches
+//                   them first.  Their producer lane acquires the neighbour's flag
+//                   for the current level before the first TMA load; their consumer
+//                   warps store every freshly computed face value locally AND into
+//                   the neighbour's ghost layer (plain st.global on peer-mapped
+//                   addresses: NVLink 5 / NVSwitch P2P); the last face CTA to finish
+//                   releases the flags for the next level (st.release.sys).  The
+//                   remaining CTAs stream the interior while those stores fly.
+//  * `shell_compute` — one-thread-per-node path over a box list; used by the
+//                   plain `box_step_kernel` (NCCL baseline's thin boxes, numerics checks).
 #pragma once
 #include "ptx.cuh"
 #include "stencil_core.h"
@@ -76,7 +80,8 @@ struct alignas(64) StepParams {
   TileGeom tile;
   // shell
   BoxTable boxes;
-  int n_shell_ctas;
+  int n_face_ctas;        // CTAs whose tile touches a face with a neighbour (numbered first)
+  const int* order;       // block index -> tile index (face CTAs first), nullptr = identity
   int use_flags;
   PeerDev peer[6];
   const unsigned long long* flags_in;
@@ -156,79 +161,114 @@ __device__ __forceinline__ long long gidx(const Geometry& g, int i, int j, int k
   return (long long)k * g.plane + (long long)j * g.pitch + g.xoff + i;
 }
 
-// first/stride: this thread's first linear node id and the stride between its nodes
-__device__ void shell_compute(const StepParams& P, long long first, long long stride, bool push,
-                              double& mx, double& s2) {
+// first/stride: this thread's first linear node id and the stride between its nodes.
+// Nodes are handled in batches of kShellBatch with all loads issued before any use:
+// the shell is latency-bound (scattered 8-byte accesses), so memory-level parallelism
+// per thread is what shortens the critical path in front of the flag release.
+constexpr int kShellBatch = 4;
+
+__device__ void shell_compute(const StepParams& P, long long first, long long stride, long long total,
+                              bool push, double& mx, double& s2) {
   const Geometry& g = P.g;
   const BoxTable& B = P.boxes;
-  const long long total = B.prefix[B.nboxes];
   const bool want_err = P.err.out != nullptr;
   const double ct = P.ct_ptr ? __ldg(P.ct_ptr) : P.ct;
-  for (long long id = first; id < total; id += stride) {
-    int b = 0;
-    while (b + 1 < B.nboxes && id >= B.prefix[b + 1]) ++b;
-    long long l = id - B.prefix[b];
-    const int ex = B.ext[b][0], ey = B.ext[b][1];
-    const int i = B.lo[b][0] + (int)(l % ex);
-    l /= ex;
-    const int j = B.lo[b][1] + (int)(l % ey);
-    const int k = B.lo[b][2] + (int)(l / ey);
-    const long long o = gidx(g, i, j, k);
-    const double* c = P.cur + o;
-    const double v = w3d_node(c[0], P.nxt[o], c[-1], c[1], c[-g.pitch], c[g.pitch], c[-g.plane],
-                              c[g.plane], P.a, P.b, P.cx, P.cy, P.cz);
-    P.nxt[o] = v;
-    if (push) {
-      const int co[3] = {i, j, k};
+  for (long long base = first; base < total; base += (long long)kShellBatch * stride) {
+    int ci[kShellBatch], cj[kShellBatch], ck[kShellBatch];
+    long long off[kShellBatch];
+    bool live[kShellBatch];
+    double c0[kShellBatch], pv[kShellBatch], xm[kShellBatch], xp[kShellBatch], ym[kShellBatch],
+        yp[kShellBatch], zm[kShellBatch], zp[kShellBatch];
 #pragma unroll
-      for (int d = 0; d < 3; ++d) {
+    for (int u = 0; u < kShellBatch; ++u) {
+      const long long id = base + (long long)u * stride;
+      live[u] = id < total;
+      int b = 0;
+      while (b + 1 < B.nboxes && id >= B.prefix[b + 1]) ++b;
+      long long l = live[u] ? id - B.prefix[b] : 0;
+      const int ex = B.ext[b][0], ey = B.ext[b][1];
+      ci[u] = B.lo[b][0] + (int)(l % ex);
+      l /= ex;
+      cj[u] = B.lo[b][1] + (int)(l % ey);
+      ck[u] = B.lo[b][2] + (int)(l / ey);
+      off[u] = gidx(g, ci[u], cj[u], ck[u]);
+    }
 #pragma unroll
-        for (int s = 0; s < 2; ++s) {
-          const PeerDev& pr = P.peer[d * 2 + s];
-          if (pr.active && co[d] == (s == 0 ? 1 : g.n[d])) {
-            int q[3] = {i, j, k};
-            q[d] = pr.ghost_index;
-            pr.field[(long long)q[2] * pr.plane + (long long)q[1] * pr.pitch + g.xoff + q[0]] = v;
+    for (int u = 0; u < kShellBatch; ++u) {
+      if (live[u]) {
+        const double* c = P.cur + off[u];
+        c0[u] = c[0];
+        xm[u] = c[-1];
+        xp[u] = c[1];
+        ym[u] = c[-g.pitch];
+        yp[u] = c[g.pitch];
+        zm[u] = c[-g.plane];
+        zp[u] = c[g.plane];
+        pv[u] = P.nxt[off[u]];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kShellBatch; ++u) {
+      if (!live[u]) continue;
+      const int i = ci[u], j = cj[u], k = ck[u];
+      const double v = w3d_node(c0[u], pv[u], xm[u], xp[u], ym[u], yp[u], zm[u], zp[u], P.a, P.b, P.cx, P.cy, P.cz);
+      P.nxt[off[u]] = v;
+      if (push) {
+        const int co[3] = {i, j, k};
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+#pragma unroll
+          for (int sd = 0; sd < 2; ++sd) {
+            const PeerDev& pr = P.peer[d * 2 + sd];
+            if (pr.active && co[d] == (sd == 0 ? 1 : g.n[d])) {
+              int q[3] = {i, j, k};
+              q[d] = pr.ghost_index;
+              pr.field[(long long)q[2] * pr.plane + (long long)q[1] * pr.pitch + g.xoff + q[0]] = v;
+            }
           }
         }
       }
-    }
-    if (want_err) {
-      const double e = w3d_abs_err(v, P.sx[i] * P.sy[j], P.sz[k] * ct);
-      mx = fmax(mx, e);
-      s2 = fma(e, e, s2);
-    }
-  }
-}
-
-__device__ void shell_wait_flags(const StepParams& P) {
-  if (threadIdx.x < 6) {
-    const int f = threadIdx.x;
-    if (P.peer[f].active) {
-      const unsigned long long t0 = globaltimer_ns();
-      unsigned spins = 0;
-      while (ld_acquire_sys(P.flags_in + f) < P.level) {
-        if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > P.timeout_ns) {
-          atomicExch(P.status, 0x100u + (unsigned)f);   // watchdog: neighbour never arrived
-          break;
-        }
+      if (want_err) {
+        const double e = w3d_abs_err(v, P.sx[i] * P.sy[j], P.sz[k] * ct);
+        mx = fmax(mx, e);
+        s2 = fma(e, e, s2);
       }
     }
   }
-  __syncthreads();
 }
 
-__device__ void shell_release_flags(const StepParams& P) {
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence_system();
-    const unsigned done = atomicAdd(P.shell_counter, 1u);
-    if (done == (unsigned)P.n_shell_ctas - 1u) {
-      *P.shell_counter = 0u;
-      __threadfence_system();
-      for (int f = 0; f < 6; ++f)
-        if (P.peer[f].active) st_release_sys(P.peer[f].flag, P.level + 1ull);
+constexpr int kPipeBarrier = 2;        // named barrier id: consumers + producer warp
+constexpr int kConsBarrier = 3;        // named barrier id: consumer warps only
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// Spin (bounded) until the neighbours named in `mask` have delivered level P.level.
+__device__ void wait_peer_flags(const StepParams& P, int mask) {
+  for (int f = 0; f < 6; ++f) {
+    if (!(mask & (1 << f))) continue;
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned spins = 0;
+    while (ld_acquire_sys(P.flags_in + f) < P.level) {
+      if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > P.timeout_ns) {
+        atomicExch(P.status, 0x100u + (unsigned)f);   // watchdog: neighbour never arrived
+        break;
+      }
     }
+  }
+}
+
+// Called by ONE thread of a face CTA after all of the CTA's stores are ordered before
+// it (CTA-scope barrier).  The last face CTA publishes level+1 to every neighbour.
+__device__ void face_cta_done(const StepParams& P) {
+  __threadfence_system();
+  const unsigned done = atomicAdd(P.shell_counter, 1u);
+  if (done == (unsigned)P.n_face_ctas - 1u) {
+    *P.shell_counter = 0u;
+    __threadfence_system();
+    for (int f = 0; f < 6; ++f)
+      if (P.peer[f].active) st_release_sys(P.peer[f].flag, P.level + 1ull);
   }
 }
 
@@ -245,7 +285,7 @@ struct TileCfg {
   static constexpr int kW = TX + 4;
   static constexpr int kHaloRows = kTY + 2;
   static constexpr int kConsumers = TX * RG;
-  static constexpr int kThreads = kConsumers + 32;
+  static constexpr int kThreads = kConsumers + 32;   // consumers + producer warp
   static constexpr int kHaloBytes = kW * kHaloRows * 8;
   static constexpr int kHaloBytesPad = (kHaloBytes + 127) / 128 * 128;
   static constexpr int kCoreBytes = TX * kTY * 8;
@@ -257,21 +297,76 @@ struct TileCfg {
   static_assert(2 * STAGES * 8 <= 128, "barrier area");
 };
 
+// faces of the block that the tile (tx,ty,ch) touches and that have a neighbour: bit axis*2+side
+__device__ __forceinline__ int tile_face_mask(const StepParams& P, int x0, int y0, int z0, int z1, int tx_w,
+                                              int ty_w) {
+  if (!P.use_flags) return 0;
+  int m = 0;
+  const int lo[3] = {x0, y0, z0}, hi[3] = {x0 + tx_w, y0 + ty_w, z1};
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    if (P.peer[d * 2].active && lo[d] <= 1 && hi[d] > 1) m |= 1 << (d * 2);
+    if (P.peer[d * 2 + 1].active && lo[d] <= P.g.n[d] && hi[d] > P.g.n[d]) m |= 1 << (d * 2 + 1);
+  }
+  return m;
+}
+
+// After a face CTA has written its tile, its consumer threads copy the tile's face
+// layers out of the local array (just written: L2 hits) into the neighbours' ghost
+// layers.  Keeping this out of the streaming loop leaves that loop identical for face
+// and interior CTAs.  tid/nthreads: consumer thread index and count.
+__device__ void face_copy_out(const StepParams& P, int mask, int x0, int y0, int z0, int z1, int tx_w, int ty_w,
+                              int tid, int nthreads) {
+  const Geometry& g = P.g;
+  const TileGeom& T = P.tile;
+  // clip the tile to the box it updates
+  const int xl = max(x0, T.lo[0]), xh = min(x0 + tx_w, T.hi[0]);
+  const int yl = max(y0, T.lo[1]), yh = min(y0 + ty_w, T.hi[1]);
+  const int ex = xh - xl, ey = yh - yl, ez = z1 - z0;
+  if (ex <= 0 || ey <= 0 || ez <= 0) return;
+#pragma unroll 1
+  for (int f = 0; f < 6; ++f) {
+    if (!(mask & (1 << f))) continue;
+    const PeerDev& pr = P.peer[f];
+    const int d = f >> 1;
+    const int layer = (f & 1) ? g.n[d] : 1;          // my edge layer along axis d
+    // iterate the two other axes, fastest first
+    const int e0 = d == 0 ? ey : ex;                    // fast extent
+    const int e1 = d == 2 ? ey : ez;                    // slow extent
+    const int total = e0 * e1;
+    for (int base = tid; base < total; base += 4 * nthreads) {
+      double v[4];
+      long long dst[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int id = base + u * nthreads;
+        if (id < total) {
+          const int a = id % e0, b = id / e0;
+          int q[3];
+          if (d == 0) { q[0] = layer; q[1] = yl + a; q[2] = z0 + b; }
+          else if (d == 1) { q[0] = xl + a; q[1] = layer; q[2] = z0 + b; }
+          else { q[0] = xl + a; q[1] = yl + b; q[2] = layer; }
+          v[u] = __ldcg(P.nxt + gidx(g, q[0], q[1], q[2]));
+          q[d] = pr.ghost_index;
+          dst[u] = (long long)q[2] * pr.plane + (long long)q[1] * pr.pitch + g.xoff + q[0];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (base + u * nthreads < total) pr.field[dst[u]] = v[u];   // peer-mapped: goes over NVLink
+    }
+  }
+}
+
 template <class Cfg>
-__device__ void tma_role(const StepParams& P, int work, uint8_t* smem, double& mx, double& s2) {
+__device__ void tma_role(const StepParams& P, int x0, int y0, int z0, int z1, int mask, uint8_t* smem,
+                         double& mx, double& s2) {
   constexpr int TX = Cfg::kTX, RPT = Cfg::kRPT, STAGES = Cfg::kStages, W = Cfg::kW;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
   uint64_t* empty = full + STAGES;
   uint8_t* stage0 = smem + Cfg::kBarBytes;
 
   const TileGeom& T = P.tile;
-  const int tx = work % T.ntx;
-  const int ty = (work / T.ntx) % T.nty;
-  const int ch = work / (T.ntx * T.nty);
-  const int x0 = T.x0 + tx * TX;
-  const int y0 = T.lo[1] + ty * Cfg::kTY;
-  const int z0 = T.lo[2] + ch * T.zc;
-  const int z1 = min(z0 + T.zc, T.hi[2]);
   const int nzc = z1 - z0;
   const int iters = nzc + 2;
 
@@ -294,6 +389,8 @@ __device__ void tma_role(const StepParams& P, int work, uint8_t* smem, double& m
     if (leader) {
       tma_prefetch_desc(&P.map_halo);
       tma_prefetch_desc(&P.map_core);
+      // ghosts of the current level must have arrived before they are loaded
+      if (mask) wait_peer_flags(P, mask);
     }
     for (int t = 0; t < iters; ++t) {
       if (leader) {
@@ -331,7 +428,6 @@ __device__ void tma_role(const StepParams& P, int work, uint8_t* smem, double& m
     zm[r] = 0.0;
   }
   double* out_col = P.nxt + (long long)(y0 + r0) * P.g.pitch + P.g.xoff + gx;
-
   for (int t = 0; t < iters; ++t) {
     const int s = t % STAGES;
     const uint32_t ph = (uint32_t)(t / STAGES) & 1u;
@@ -374,6 +470,12 @@ __device__ void tma_role(const StepParams& P, int work, uint8_t* smem, double& m
     __syncwarp();
     if ((threadIdx.x & 31) == 0) mbar_arrive(empty + s);
   }
+  if (mask) {
+    named_bar_sync(kConsBarrier, Cfg::kConsumers);   // the tile is written (CTA-visible)
+    face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kConsumers);
+    named_bar_sync(kConsBarrier, Cfg::kConsumers);   // every consumer's peer stores are issued
+    if (threadIdx.x == 0) face_cta_done(P);
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -386,14 +488,17 @@ fused_step_kernel(const __grid_constant__ StepParams P) {
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
   double* red = reinterpret_cast<double*>(smem + 128);
   double mx = 0.0, s2 = 0.0;
-  if ((int)blockIdx.x < P.n_shell_ctas) {
-    if (P.use_flags) shell_wait_flags(P);
-    const long long nthreads = (long long)P.n_shell_ctas * blockDim.x;
-    shell_compute(P, (long long)blockIdx.x * blockDim.x + threadIdx.x, nthreads, P.use_flags != 0, mx, s2);
-    if (P.use_flags) shell_release_flags(P);
-  } else {
-    tma_role<Cfg>(P, (int)blockIdx.x - P.n_shell_ctas, smem, mx, s2);
-  }
+  const TileGeom& T = P.tile;
+  const int work = P.order ? P.order[blockIdx.x] : (int)blockIdx.x;
+  const int tx = work % T.ntx;
+  const int ty = (work / T.ntx) % T.nty;
+  const int ch = work / (T.ntx * T.nty);
+  const int x0 = T.x0 + tx * Cfg::kTX;
+  const int y0 = T.lo[1] + ty * Cfg::kTY;
+  const int z0 = T.lo[2] + ch * T.zc;
+  const int z1 = min(z0 + T.zc, T.hi[2]);
+  const int mask = tile_face_mask(P, x0, y0, z0, z1, Cfg::kTX, Cfg::kTY);
+  tma_role<Cfg>(P, x0, y0, z0, z1, mask, smem, mx, s2);
   if (P.err.out != nullptr) {
     __syncthreads();
     publish_error(P.err, mx, s2, red);
@@ -405,7 +510,7 @@ __global__ void __launch_bounds__(256) box_step_kernel(const __grid_constant__ S
   __shared__ double red[66];
   double mx = 0.0, s2 = 0.0;
   shell_compute(P, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x,
-                false, mx, s2);
+                P.boxes.prefix[P.boxes.nboxes], false, mx, s2);
   publish_error(P.err, mx, s2, red);
 }
 

@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstring>
 #include <new>
+#include <vector>
 
 using namespace w3d;
 
@@ -33,11 +34,13 @@ int fail(int code, const char* fmt, ...) {
   } while (0)
 
 // ---- TMA tile variants ------------------------------------------------------------
-//            TX  RPT RG STAGES
-using Cfg0 = TileCfg<128, 8, 1, 4>;   // 128 x 8 tile, 160 threads, ~75 KB  -> 3 CTAs / SM
-using Cfg1 = TileCfg<128, 8, 2, 3>;   // 128 x 16 tile, 288 threads, ~105 KB -> 2 CTAs / SM
-using Cfg2 = TileCfg<128, 8, 4, 3>;   // 128 x 32 tile, 544 threads, ~204 KB -> 1 CTA / SM
-using Cfg3 = TileCfg<64, 8, 4, 4>;    // 64 x 32 tile, 288 threads, ~140 KB  -> 1 CTA / SM
+//            TX  RPT RG STAGES   (+32 producer threads, +128 shell threads per CTA)
+using Cfg0 = TileCfg<128, 8, 1, 4>;   // 128 x 8 tile,  288 threads, ~76 KB  -> 2 CTAs / SM
+using Cfg1 = TileCfg<128, 8, 2, 4>;   // 128 x 16 tile, 416 threads, ~143 KB -> 1 CTA / SM
+using Cfg2 = TileCfg<128, 8, 4, 3>;   // 128 x 32 tile, 672 threads, ~207 KB -> 1 CTA / SM
+using Cfg3 = TileCfg<64, 8, 4, 4>;    // 64 x 32 tile,  416 threads, ~141 KB -> 1 CTA / SM  (default)
+using Cfg4 = TileCfg<64, 8, 4, 5>;    // 64 x 32 tile,  5-stage ring, ~176 KB -> 1 CTA / SM
+using Cfg5 = TileCfg<64, 8, 2, 6>;    // 64 x 16 tile,  288 threads, ~109 KB -> 2 CTAs / SM
 
 struct Variant {
   int tx, ty, threads, smem, ctas_per_sm;
@@ -46,17 +49,21 @@ struct Variant {
 };
 
 const Variant kVariants[] = {
-    {Cfg0::kTX, Cfg0::kTY, Cfg0::kThreads, Cfg0::kSmemBytes, 3, fused_step_kernel<Cfg0, 3>, "128x8x4st"},
-    {Cfg1::kTX, Cfg1::kTY, Cfg1::kThreads, Cfg1::kSmemBytes, 2, fused_step_kernel<Cfg1, 2>, "128x16x3st"},
+    {Cfg0::kTX, Cfg0::kTY, Cfg0::kThreads, Cfg0::kSmemBytes, 2, fused_step_kernel<Cfg0, 2>, "128x8x4st"},
+    {Cfg1::kTX, Cfg1::kTY, Cfg1::kThreads, Cfg1::kSmemBytes, 1, fused_step_kernel<Cfg1, 1>, "128x16x4st"},
     {Cfg2::kTX, Cfg2::kTY, Cfg2::kThreads, Cfg2::kSmemBytes, 1, fused_step_kernel<Cfg2, 1>, "128x32x3st"},
     {Cfg3::kTX, Cfg3::kTY, Cfg3::kThreads, Cfg3::kSmemBytes, 1, fused_step_kernel<Cfg3, 1>, "64x32x4st"},
+    {Cfg4::kTX, Cfg4::kTY, Cfg4::kThreads, Cfg4::kSmemBytes, 1, fused_step_kernel<Cfg4, 1>, "64x32x5st"},
+    {Cfg5::kTX, Cfg5::kTY, Cfg5::kThreads, Cfg5::kSmemBytes, 2, fused_step_kernel<Cfg5, 2>, "64x16x6st"},
 };
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 constexpr int kDefaultVariant = 3;   // best of the measured sweep at 512^3 (profiles/variant_sweep.md)
 
 // ---- workspace layout ---------------------------------------------------------------
-constexpr size_t kCounterBytes = 256;   // tickets [0..7] at 0, shell counter at +64
+constexpr size_t kCounterBytes = 256;   // tickets [0..7] at 0, face-CTA counter at +64
+constexpr size_t kOrderBytes = (size_t)W3D_MAX_PARTIALS * sizeof(int);   // block -> tile table
 constexpr size_t kSlotBytes = 2ull * W3D_MAX_PARTIALS * sizeof(double);
+constexpr size_t kSlotBase = kCounterBytes + kOrderBytes;
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
@@ -84,11 +91,11 @@ struct W3dPlan {
   int num_sms;
   CUtensorMap halo[2], core[2];    // per field array
   bool maps_ok;
-  // fused geometry
-  int ilo[3], ihi[3];
-  BoxTable shell;
-  int n_shell_ctas;
-  TileGeom tile;                   // interior
+  // fused geometry: the TMA role covers the whole block; CTAs that touch a face
+  // with a neighbour come first in `order`
+  TileGeom tile;
+  int n_ctas, n_face_ctas;
+  int* order_dev;                  // lives in the workspace
   bool any_peer;
   const double* ct_table;          // optional device table of cos(a_t t_n), host-fed
   long long launches;
@@ -102,7 +109,7 @@ ErrCtl err_ctl(const W3dPlan* p, int slot, double* out) {
   char* ws = static_cast<char*>(p->d.workspace);
   e.out = out;
   e.ticket = reinterpret_cast<unsigned*>(ws) + slot;
-  e.part_max = reinterpret_cast<double*>(ws + kCounterBytes + (size_t)slot * kSlotBytes);
+  e.part_max = reinterpret_cast<double*>(ws + kSlotBase + (size_t)slot * kSlotBytes);
   e.part_sum = e.part_max + W3D_MAX_PARTIALS;
   return e;
 }
@@ -214,7 +221,7 @@ extern "C" {
 
 const char* w3d_last_error(void) { return g_err; }
 const char* w3d_version(void) { return "wave3d-b200 1.0 (sm_100a)"; }
-size_t w3d_workspace_bytes(void) { return kCounterBytes + (size_t)W3D_ERR_SLOTS * kSlotBytes; }
+size_t w3d_workspace_bytes(void) { return kSlotBase + (size_t)W3D_ERR_SLOTS * kSlotBytes; }
 size_t w3d_error_workspace_bytes(void) { return kCounterBytes + kSlotBytes; }
 
 int64_t w3d_pitch_for(int32_t nx) {
@@ -253,30 +260,44 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
   p->maps_ok = false;
   p->launches = 0;
   p->ct_table = nullptr;
-  // interior / shell split
   p->any_peer = false;
-  for (int d = 0; d < 3; ++d) {
-    p->ilo[d] = 1 + (desc->peer[d * 2].active ? 1 : 0);
-    p->ihi[d] = std::max(p->ilo[d], b.n[d] + 1 - (desc->peer[d * 2 + 1].active ? 1 : 0));
-    p->any_peer = p->any_peer || desc->peer[d * 2].active || desc->peer[d * 2 + 1].active;
-  }
-  std::memset(&p->shell, 0, sizeof(p->shell));
+  for (int f = 0; f < 6; ++f) p->any_peer = p->any_peer || desc->peer[f].active;
+  const Variant& v = kVariants[p->variant];
   {
-    int lo[3] = {1, 1, 1}, hi[3] = {b.n[0] + 1, b.n[1] + 1, b.n[2] + 1};
-    for (int d = 2; d >= 0; --d) {
-      int l2[3] = {lo[0], lo[1], lo[2]}, h2[3] = {hi[0], hi[1], hi[2]};
-      if (p->ilo[d] > lo[d]) { h2[d] = p->ilo[d]; add_box(&p->shell, l2, h2); h2[d] = hi[d]; }
-      if (p->ihi[d] < hi[d]) { l2[d] = p->ihi[d]; add_box(&p->shell, l2, h2); }
-      lo[d] = p->ilo[d];
-      hi[d] = p->ihi[d];
+    const int lo[3] = {1, 1, 1}, hi[3] = {b.n[0] + 1, b.n[1] + 1, b.n[2] + 1};
+    plan_tiles(p, lo, hi, desc->zchunk, &p->tile);
+  }
+  p->n_ctas = p->tile.ntx * p->tile.nty * p->tile.nchunks;
+  if (p->n_ctas > W3D_MAX_PARTIALS) {
+    const int need = p->n_ctas;
+    delete p;
+    return fail(W3D_EINVAL, "block needs %d CTAs, limit %d: raise zchunk", need, W3D_MAX_PARTIALS);
+  }
+  // block index -> tile index: tiles that touch a face with a neighbour first (the hardware
+  // dispatches blocks in index order), so the exchange starts at the top of the kernel
+  p->order_dev = reinterpret_cast<int*>(static_cast<char*>(desc->workspace) + kCounterBytes);
+  {
+    std::vector<int> face, rest;
+    const TileGeom& t = p->tile;
+    for (int w = 0; w < p->n_ctas; ++w) {
+      const int tx = w % t.ntx, ty = (w / t.ntx) % t.nty, ch = w / (t.ntx * t.nty);
+      const int lo[3] = {t.x0 + tx * v.tx, t.lo[1] + ty * v.ty, t.lo[2] + ch * t.zc};
+      const int hi[3] = {lo[0] + v.tx, lo[1] + v.ty, std::min(lo[2] + t.zc, t.hi[2])};
+      bool is_face = false;
+      for (int d = 0; d < 3; ++d) {
+        if (desc->peer[d * 2].active && lo[d] <= 1 && hi[d] > 1) is_face = true;
+        if (desc->peer[d * 2 + 1].active && lo[d] <= b.n[d] && hi[d] > b.n[d]) is_face = true;
+      }
+      (is_face ? face : rest).push_back(w);
+    }
+    p->n_face_ctas = (int)face.size();
+    face.insert(face.end(), rest.begin(), rest.end());
+    cudaError_t ce = cudaMemcpy(p->order_dev, face.data(), face.size() * sizeof(int), cudaMemcpyHostToDevice);
+    if (ce != cudaSuccess) {
+      delete p;
+      return fail(W3D_ECUDA, "cudaMemcpy(order table): %s", cudaGetErrorString(ce));
     }
   }
-  const Variant& v = kVariants[p->variant];
-  const long long shell_nodes = p->shell.prefix[p->shell.nboxes];
-  p->n_shell_ctas = shell_nodes == 0 ? 0
-      : (int)std::min<long long>((shell_nodes + (long long)v.threads * 4 - 1) / ((long long)v.threads * 4),
-                                 (long long)p->num_sms * 2);
-  plan_tiles(p, p->ilo, p->ihi, desc->zchunk, &p->tile);
   cudaError_t e = cudaFuncSetAttribute(v.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v.smem);
   if (e != cudaSuccess) {
     delete p;
@@ -285,12 +306,10 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
   int rc = encode_maps(p);
   if (rc != W3D_OK) { delete p; return rc; }
   snprintf(p->text, sizeof(p->text),
-           "block %dx%dx%d pitch %lld | variant %s (%d thr, %d B smem, %d CTA/SM) | interior [%d,%d)x[%d,%d)x[%d,%d) "
-           "tiles %dx%d zc %d chunks %d -> %lld CTAs | shell %lld nodes in %d boxes, %d CTAs | SMs %d",
-           b.n[0], b.n[1], b.n[2], (long long)b.pitch, v.name, v.threads, v.smem, v.ctas_per_sm, p->ilo[0], p->ihi[0],
-           p->ilo[1], p->ihi[1], p->ilo[2], p->ihi[2], p->tile.ntx, p->tile.nty, p->tile.zc, p->tile.nchunks,
-           (long long)p->tile.ntx * p->tile.nty * p->tile.nchunks, shell_nodes, p->shell.nboxes, p->n_shell_ctas,
-           p->num_sms);
+           "block %dx%dx%d pitch %lld | variant %s (%d thr, %d B smem, %d CTA/SM) | tiles %dx%d zc %d chunks %d -> "
+           "%d CTAs, %d of them face CTAs (numbered first, push halos over P2P) | SMs %d",
+           b.n[0], b.n[1], b.n[2], (long long)b.pitch, v.name, v.threads, v.smem, v.ctas_per_sm, p->tile.ntx,
+           p->tile.nty, p->tile.zc, p->tile.nchunks, p->n_ctas, p->n_face_ctas, p->num_sms);
   *out = p;
   return W3D_OK;
 }
@@ -326,8 +345,8 @@ int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double 
   fill_common(p, &P, s, a, b, cscale, ct);
   P.err = err_ctl(p, 0, err_out);
   P.tile = p->tile;
-  P.boxes = p->shell;
-  P.n_shell_ctas = p->n_shell_ctas;
+  P.order = p->order_dev;
+  P.n_face_ctas = p->n_face_ctas;
   P.use_flags = p->any_peer ? 1 : 0;
   const int nxt = (s & 1) ^ 1;
   for (int f = 0; f < 6; ++f) {
@@ -341,8 +360,7 @@ int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double 
   }
   P.flags_in = p->d.flags_in;
   P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
-  const int nblocks = p->n_shell_ctas + p->tile.ntx * p->tile.nty * p->tile.nchunks;
-  return launch_fused(p, P, nblocks, static_cast<cudaStream_t>(stream));
+  return launch_fused(p, P, p->n_ctas, static_cast<cudaStream_t>(stream));
 }
 
 int w3d_step_tma(W3dPlan* p, int s, double a, double b, double cscale, double ct, const int32_t lo[3],
@@ -359,7 +377,8 @@ int w3d_step_tma(W3dPlan* p, int s, double a, double b, double cscale, double ct
     if (l[d] < 1 || h[d] > p->g.n[d] + 1) return fail(W3D_EINVAL, "box outside the block");
   }
   plan_tiles(p, l, h, p->d.zchunk, &P.tile);
-  P.n_shell_ctas = 0;
+  P.n_face_ctas = 0;
+  P.order = nullptr;
   P.use_flags = 0;
   const int nblocks = P.tile.ntx * P.tile.nty * P.tile.nchunks;
   if (nblocks == 0 && err_out) {

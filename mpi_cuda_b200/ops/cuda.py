@@ -153,6 +153,9 @@ class CudaPlan:
         d.workspace_bytes = workspace.numel() * workspace.element_size()
         d.variant, d.zchunk, d.num_sms, d.spin_timeout_ms = variant, zchunk, 0, spin_timeout_ms
         self._desc = d
+        # plan creation copies a small table into the workspace with a blocking copy: make sure
+        # the fills that created the tensors (possibly on another stream) are done first
+        torch.cuda.synchronize()
         h = C.c_void_p()
         check(lib().w3d_plan_create(C.byref(d), C.byref(h)))
         self._h = h

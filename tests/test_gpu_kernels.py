@@ -71,7 +71,7 @@ def test_init_kernel_matches_tables():
     assert float(ops.f[1].abs().max()) == 0.0
 
 
-@pytest.mark.parametrize("kernel,variant", [("box", -1), ("tma", 0), ("tma", 1), ("tma", 2), ("tma", 3)])
+@pytest.mark.parametrize("kernel,variant", [("box", -1), ("tma", 0), ("tma", 1), ("tma", 2), ("tma", 3), ("tma", 4), ("tma", 5)])
 @pytest.mark.parametrize("N", [(33, 19, 11), (130, 37, 45), (257, 40, 23)])
 def test_step_kernels_bit_exact_vs_cpu(kernel, variant, N):
     p = WaveProblem(N, 1.0, 1e-3, 5)
