@@ -62,6 +62,11 @@ struct ErrCtl {
   double* part_max;
   double* part_sum;
   unsigned* ticket;
+  // cross-GPU part of the reduction: the same (max, sum) pair is also stored into this
+  // rank's row of every other rank's table (peer-mapped addresses, NVLink P2P), so after
+  // the time loop every rank already holds all partials — no collective, no host.
+  int n_bcast;
+  double* bcast[7];
 };
 
 struct alignas(64) StepParams {
@@ -148,6 +153,10 @@ __device__ void publish_error(const ErrCtl& e, double mx, double s2, double* red
       if (lane == 0) {
         e.out[0] = m;
         e.out[1] = s;
+        for (int q = 0; q < e.n_bcast; ++q) {
+          e.bcast[q][0] = m;
+          e.bcast[q][1] = s;
+        }
         *e.ticket = 0u;   // ready for the next launch on this slot
       }
     }

@@ -111,6 +111,7 @@ ErrCtl err_ctl(const W3dPlan* p, int slot, double* out) {
   e.ticket = reinterpret_cast<unsigned*>(ws) + slot;
   e.part_max = reinterpret_cast<double*>(ws + kSlotBase + (size_t)slot * kSlotBytes);
   e.part_sum = e.part_max + W3D_MAX_PARTIALS;
+  e.n_bcast = 0;
   return e;
 }
 
@@ -344,6 +345,11 @@ int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double 
   StepParams P;
   fill_common(p, &P, s, a, b, cscale, ct);
   P.err = err_ctl(p, 0, err_out);
+  if (err_out && p->d.err_table && p->d.n_err_peers > 0) {
+    const ptrdiff_t off = err_out - p->d.err_table;   // same offset in every rank's table
+    P.err.n_bcast = std::min(p->d.n_err_peers, 7);
+    for (int q = 0; q < P.err.n_bcast; ++q) P.err.bcast[q] = p->d.err_table_peer[q] + off;
+  }
   P.tile = p->tile;
   P.order = p->order_dev;
   P.n_face_ctas = p->n_face_ctas;
@@ -472,6 +478,7 @@ int w3d_error_norms(const double* u, const W3dBlock* blk, const double* sx, cons
   e.ticket = reinterpret_cast<unsigned*>(ws);
   e.part_max = reinterpret_cast<double*>(ws + kCounterBytes);
   e.part_sum = e.part_max + W3D_MAX_PARTIALS;
+  e.n_bcast = 0;
   const long long rows = (long long)g.n[1] * g.n[2];
   const int blocks = (int)std::max<long long>(1, std::min<long long>((rows + 7) / 8, 148 * 8));
   error_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(u, g, sx, sy, sz, ct, e);

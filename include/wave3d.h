@@ -63,7 +63,15 @@ typedef struct W3dPlanDesc {
   int32_t variant;              /* TMA tile variant, -1 = auto */
   int32_t zchunk;               /* planes per CTA in the z-marching kernel, 0 = auto */
   int32_t num_sms;              /* 0 = query the current device */
-  int32_t spin_timeout_ms;      /* watchdog for flag waits, 0 = 2000 */
+  int32_t spin_timeout_ms;      /* watchdog for flag waits, 0 = 10000 */
+  /* Cross-GPU error reduction (optional).  Every rank owns a table of identical layout;
+   * err_table is mine, err_table_peer[q] are the other ranks' tables mapped into this
+   * process.  When w3d_step_fused is given err_out inside err_table, the kernel stores
+   * the pair at the same offset of every peer table as well (MPI_Reduce replacement:
+   * report.pdf p.15-16 shows rank 0 printing global errors each reporting step). */
+  double* err_table;
+  double* err_table_peer[7];
+  int32_t n_err_peers;
 } W3dPlanDesc;
 
 typedef struct W3dPlan W3dPlan;
@@ -96,11 +104,13 @@ int w3d_plan_init(W3dPlan* plan, void* stream);
  * the nodes it updates into err_out[0..1] (exact = sx*sy*sz*ct), using reduction
  * slot `slot` of the workspace.
  *
- * w3d_step_fused: ONE launch.  CTAs with low block indices compute the shell
- *   (nodes adjacent to a face with a neighbour) after acquiring the neighbours'
- *   flags for level s, store the results locally and straight into the
- *   neighbours' ghost layers (NVLink P2P), and the last shell CTA releases the
- *   flags for level s+1; the remaining CTAs stream the interior with TMA.
+ * w3d_step_fused: ONE launch over the whole block.  CTAs whose tile touches a face
+ *   with a neighbour are numbered (hence dispatched) first: they acquire the
+ *   neighbours' flags for level s before loading, stream their tile with TMA like
+ *   every other CTA, then copy the freshly written face layers straight into the
+ *   neighbours' ghost layers (NVLink P2P stores); the last of them releases the
+ *   flags for level s+1.  The remaining CTAs stream the interior meanwhile.  The
+ *   error pair is also broadcast into the peers' tables (see W3dPlanDesc).
  * w3d_step_tma: the TMA z-marching kernel on the box [lo,hi) only, no communication.
  * w3d_step_box: the plain one-thread-per-node kernel on the box [lo,hi), no
  *   communication (used by the NCCL baseline for the shell and as a numerics check). */

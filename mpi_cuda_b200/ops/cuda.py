@@ -35,7 +35,8 @@ class W3dPlanDesc(C.Structure):
                 ("coef", C.c_double * 3), ("peer", W3dPeer * 6), ("flags_in", C.c_void_p),
                 ("status", C.c_void_p), ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
                 ("variant", C.c_int32), ("zchunk", C.c_int32), ("num_sms", C.c_int32),
-                ("spin_timeout_ms", C.c_int32)]
+                ("spin_timeout_ms", C.c_int32), ("err_table", C.c_void_p), ("err_table_peer", C.c_void_p * 7),
+                ("n_err_peers", C.c_int32)]
 
 
 class CudaLibError(RuntimeError):
@@ -123,7 +124,8 @@ class CudaPlan:
     def __init__(self, n: Sequence[int], fields: Sequence[torch.Tensor], tables: Sequence[torch.Tensor],
                  coef: Sequence[float], flags_in: torch.Tensor, status: torch.Tensor,
                  workspace: torch.Tensor, peers: Optional[dict] = None, variant: int = -1,
-                 zchunk: int = 0, spin_timeout_ms: int = 0):
+                 zchunk: int = 0, spin_timeout_ms: int = 0, err_table_ptr: int = 0,
+                 err_table_peer_ptrs: Sequence[int] = ()):
         self.n = tuple(int(x) for x in n)
         self.blk = make_block(self.n)
         self.fields = list(fields)
@@ -152,6 +154,13 @@ class CudaPlan:
         d.workspace = workspace.data_ptr()
         d.workspace_bytes = workspace.numel() * workspace.element_size()
         d.variant, d.zchunk, d.num_sms, d.spin_timeout_ms = variant, zchunk, 0, spin_timeout_ms
+        if err_table_ptr and err_table_peer_ptrs:
+            if len(err_table_peer_ptrs) > 7:
+                raise ValueError("at most 7 peer error tables (8 GPUs per node)")
+            d.err_table = err_table_ptr
+            for q, ptr in enumerate(err_table_peer_ptrs):
+                d.err_table_peer[q] = ptr
+            d.n_err_peers = len(err_table_peer_ptrs)
         self._desc = d
         # plan creation copies a small table into the workspace with a blocking copy: make sure
         # the fills that created the tensors (possibly on another stream) are done first

@@ -58,7 +58,11 @@ class FusedSolver:
         blk = self.blk
         fbytes = max(_field_bytes(b.n) for b in blocks)
         fbytes = (fbytes + 255) // 256 * 256
-        total = _FLAG_BYTES + 2 * fbytes
+        # error table: one row per rank, (K+1) x (max, sum sq); every rank holds a full copy
+        # that the other ranks' kernels fill over NVLink
+        tbytes = (self.world * (p.K + 1) * 16 + 255) // 256 * 256
+        f0 = _FLAG_BYTES + tbytes                     # offset of the first field array
+        total = f0 + 2 * fbytes
         # ---- storage: symmetric when there are real peers ----
         self.symm = None
         if self.world > 1:
@@ -74,12 +78,14 @@ class FusedSolver:
         shape = cuda.field_shape(blk.n)
         nel = shape[0] * shape[1] * shape[2]
         self.flags = buf[:_FLAG_BYTES].view(torch.int64)
-        self.f = [buf[_FLAG_BYTES + q * fbytes: _FLAG_BYTES + q * fbytes + nel * 8].view(torch.float64).view(shape)
+        self.f = [buf[f0 + q * fbytes: f0 + q * fbytes + nel * 8].view(torch.float64).view(shape)
                   for q in range(2)]
+        self.table = buf[_FLAG_BYTES: _FLAG_BYTES + self.world * (p.K + 1) * 16].view(torch.float64).view(
+            self.world, p.K + 1, 2)
         self.tab = [torch.from_numpy(t).to(self.device) for t in local_tables(p, blk)]
         self.status = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.ws = torch.zeros(cuda.workspace_bytes(), dtype=torch.uint8, device=self.device)
-        self.trace = torch.zeros((p.K + 1, 2), dtype=torch.float64, device=self.device)
+        self.trace = self.table[self.rank]            # my row: the kernel writes it here and in every peer's copy
         # ---- peers ----
         peers: Dict[int, cuda.PeerSpec] = {}
         for d in range(3):
@@ -93,11 +99,14 @@ class FusedSolver:
                 ghost = pb.n[d] + 1 if s == 0 else 0
                 base = base_ptrs[r] if self.world > 1 else base_ptrs[0]
                 peers[d * 2 + s] = cuda.PeerSpec(
-                    field_ptrs=(base + _FLAG_BYTES, base + _FLAG_BYTES + fbytes), ghost_index=ghost,
+                    field_ptrs=(base + f0, base + f0 + fbytes), ghost_index=ghost,
                     pitch=pshape[2], plane=pshape[1] * pshape[2],
                     flag_ptr=base + 8 * (d * 2 + (1 - s)))
         self.plan = cuda.CudaPlan(blk.n, self.f, self.tab, p.coeffs(), self.flags, self.status, self.ws,
-                                  peers=peers, variant=variant, zchunk=zchunk, spin_timeout_ms=spin_timeout_ms)
+                                  peers=peers, variant=variant, zchunk=zchunk, spin_timeout_ms=spin_timeout_ms,
+                                  err_table_ptr=base_ptrs[self.rank if self.world > 1 else 0] + _FLAG_BYTES,
+                                  err_table_peer_ptrs=[base_ptrs[r] + _FLAG_BYTES for r in range(self.world)
+                                                       if r != self.rank] if self.world > 1 else [])
         self.ct = time_table(p)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.kernel_launches = 0
@@ -117,7 +126,7 @@ class FusedSolver:
         All ranks must have finished this before any rank's first step may push
         into their ghosts, hence the barrier."""
         self.plan.init()
-        self.trace.zero_()
+        self.trace.zero_()                               # only my own row: peers clear theirs
         self.barrier()
 
     def step(self, n: int, want_err: bool = True) -> None:
@@ -160,19 +169,16 @@ class FusedSolver:
                                "a neighbour's halo flag never arrived")
 
     def gather_trace(self) -> List[Tuple[int, float, float, float]]:
-        """Combine the per-rank (max, sum sq) rows: one all-gather after the loop."""
-        t = self.trace
-        if self.world > 1:
-            allt = [torch.empty_like(t) for _ in range(self.world)]
-            dist.all_gather(allt, t, group=self.group)
-            st = torch.stack(allt)                       # (world, K+1, 2)
-            mx = st[:, :, 0].max(dim=0).values
-            s2 = st[:, :, 1].cpu().double()
-            s2 = sum(s2[r] for r in range(self.world))   # fixed rank order
-            mx = mx.cpu()
-        else:
-            tc = t.cpu()
-            mx, s2 = tc[:, 0], tc[:, 1]
+        """Combine the per-rank (max, sum sq) rows.
+
+        Every rank's kernel has already stored its row into every other rank's table
+        (P2P stores from the error epilogue), so this is a purely local read — call it
+        after :meth:`barrier`.  The sum is taken in fixed rank order."""
+        tc = self.table.cpu()                            # (world, K+1, 2)
+        mx = tc[:, :, 0].max(dim=0).values
+        s2 = tc[0, :, 1].clone()
+        for r in range(1, self.world):
+            s2 += tc[r, :, 1]
         p = self.p
         return [(n, n * p.tau, float(mx[n]), math.sqrt(float(s2[n]) / p.n_unknowns))
                 for n in range(1, p.K + 1) if n % self.every == 0]
@@ -213,6 +219,57 @@ class FusedSolver:
     def field(self, parity: int) -> torch.Tensor:
         xo = cuda.XOFF + 1
         return self.f[parity][1:-1, 1:-1, xo: xo + self.blk.n[0]].contiguous()
+
+    # -- tracing ---------------------------------------------------------------
+    def profile_steps(self) -> List[float]:
+        """Device time of every step (ms, CUDA events, eager launches; max over ranks).
+
+        The per-step counterpart of the reference's summed phase timers (report.pdf
+        p.16 §4.4); feed the result to ``utils.timing.write_chrome_trace``."""
+        self.init()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(self.p.K + 1)]
+        ev[0].record()
+        for n in range(1, self.p.K + 1):
+            self.step(n, n % self.every == 0)
+            ev[n].record()
+        self.barrier()
+        ms = torch.tensor([ev[n - 1].elapsed_time(ev[n]) for n in range(1, self.p.K + 1)],
+                          dtype=torch.float64, device=self.device)
+        if self.world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=self.group)
+        return [float(v) for v in ms.cpu()]
+
+    # -- checkpoint / restart ----------------------------------------------------
+    def run_range(self, first: int, last: int) -> None:
+        """Eagerly run steps first..last (levels first-1 -> last)."""
+        self._enqueue_steps(first, last)
+
+    def save_checkpoint(self, path: str, level: int) -> str:
+        """Dump both local arrays (ghosts included) after time level ``level``."""
+        from ..utils import checkpoint
+        self.barrier()
+        meta = {"N": self.p.N, "L": self.p.L, "tau": self.p.tau, "K": self.p.K, "bc": self.p.bc,
+                "dims": self.dims, "rank": self.rank, "n": self.blk.n}
+        out = checkpoint.save_state(path, self.rank, level, self.f, meta)
+        self.barrier()
+        return out
+
+    def load_checkpoint(self, path: str) -> int:
+        """Restore a dump; returns the level to continue from (next step = level + 1)."""
+        from ..utils import checkpoint
+        st = checkpoint.load_state(path, self.rank)
+        m = st["meta"]
+        if tuple(m["N"]) != self.p.N or tuple(m["dims"]) != self.dims or m["bc"] != self.p.bc or \
+                tuple(m["n"]) != self.blk.n or abs(m["tau"] - self.p.tau) > 0:
+            raise ValueError(f"checkpoint {path} does not match this problem/decomposition: {m}")
+        level = int(st["level"])
+        self.plan.init()                       # clears status, counters
+        for dst, src in zip(self.f, st["fields"]):
+            dst.copy_(src)
+        # ghosts of `level` are part of the dump: tell the kernels they have arrived
+        self.flags[:6].fill_(level)
+        self.barrier()
+        return level
 
 
 class StreamingSession:

@@ -72,6 +72,10 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--json", action="store_true")
     ap.add_argument("--quiet", action="store_true")
     ap.add_argument("--oracle", action="store_true", help="also print the closed-form expected errors")
+    ap.add_argument("--checkpoint", metavar="PATH", help="fused backend: dump the state after --checkpoint-at steps")
+    ap.add_argument("--checkpoint-at", type=int, default=0)
+    ap.add_argument("--restart", metavar="PATH", help="fused backend: continue from a dump written by --checkpoint")
+    ap.add_argument("--trace", metavar="FILE", help="fused backend: per-step device times as a Chrome trace")
     return ap
 
 
@@ -85,6 +89,44 @@ def parse(argv: Optional[List[str]] = None) -> Tuple[WaveProblem, argparse.Names
     args.threads = threads
     p = WaveProblem(f["N"], L, f["tau"], f["K"], bc=args.bc)
     return p, args
+
+
+def _fused_session(p: WaveProblem, args, rank: int) -> int:
+    """--checkpoint / --restart / --trace: drive the fused solver step ranges directly."""
+    import torch
+    import torch.distributed as dist
+    from ..parallel.decomp import parse_dims
+    from ..parallel.fused import FusedSolver
+    from ..utils.report import format_step
+    from ..utils.timing import write_chrome_trace
+    p.check_cfl(strict=not args.no_cfl_check)
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    s = FusedSolver(p, parse_dims(args.decomp, world), every=args.report_every, variant=args.variant,
+                    zchunk=args.zchunk, use_graph=False)
+    if args.trace:
+        ms = s.profile_steps()
+        if rank == 0:
+            write_chrome_trace(args.trace, ms, rank)
+            print(f"wrote {args.trace}: {len(ms)} steps, mean {sum(ms) / len(ms):.4f} ms/step")
+    else:
+        first = 1
+        if args.restart:
+            first = s.load_checkpoint(args.restart) + 1
+        else:
+            s.init()
+        last = args.checkpoint_at if (args.checkpoint and 0 < args.checkpoint_at < p.K) else p.K
+        s.run_range(first, last)
+        if args.checkpoint and last < p.K:
+            out = s.save_checkpoint(args.checkpoint, last)
+            if rank == 0:
+                print(f"checkpoint after step {last}: {out}")
+        s.barrier()
+        s.check_status()
+    if rank == 0 and not args.quiet:
+        for r in s.gather_trace():
+            if r[2] > 0 or r[3] > 0:
+                print(format_step(*r))
+    return 0
 
 
 def main(argv: Optional[List[str]] = None) -> int:
@@ -107,6 +149,8 @@ def main(argv: Optional[List[str]] = None) -> int:
         if p.courant > 1.0:
             print(f"warning: Courant number {p.courant:.3f} > 1", file=sys.stderr)
     try:
+        if args.checkpoint or args.restart or args.trace:
+            return _fused_session(p, args, rank)
         res = solve(p, backend=args.backend, decomp=args.decomp, threads=args.threads,
                     every=args.report_every, ranks=args.ranks, verbose=not args.quiet,
                     check_cfl=not args.no_cfl_check, variant=args.variant, zchunk=args.zchunk,

@@ -198,6 +198,54 @@ def test_streaming_session_matches_batch():
         assert mx == b[2] and abs(math.sqrt(s2 / p.n_unknowns) - b[3]) <= 1e-15 * b[3]
 
 
+def test_watchdog_trips_instead_of_hanging():
+    """A halo flag that never arrives must end in an error code, not a hung GPU."""
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem(48, 2.0, 1e-3, 4, bc="ddp")
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, spin_timeout_ms=30)
+    s.init()
+    s.step(2)                     # level 1 was never produced: its flag cannot arrive
+    torch.cuda.synchronize()
+    with pytest.raises(RuntimeError, match="watchdog"):
+        s.check_status()
+    s.run()                       # the solver is usable again after a re-init
+    s.check_status()
+
+
+def test_checkpoint_restart_is_bit_exact(tmp_path):
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem((60, 44, 36), 2.0, 1e-3, 10, bc="dpd")
+    a = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
+    full = a.run().trace
+    want = a.field(p.K & 1).clone()
+    b = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
+    b.init()
+    b.run_range(1, 6)
+    ck = b.save_checkpoint(str(tmp_path / "ck"), 6)
+    assert ck.endswith(".rank0.pt")
+    c = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
+    level = c.load_checkpoint(str(tmp_path / "ck"))
+    assert level == 6
+    c.run_range(level + 1, p.K)
+    c.barrier()
+    assert torch.equal(c.field(p.K & 1), want)
+    got = c.gather_trace()
+    assert got[6:] == full[6:]
+
+
+def test_profile_steps_and_chrome_trace(tmp_path):
+    import json
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    from mpi_cuda_b200.utils.timing import write_chrome_trace
+    p = WaveProblem(96, 1.0, 1e-3, 5)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
+    ms = s.profile_steps()
+    assert len(ms) == 5 and all(0 < v < 50 for v in ms)
+    out = tmp_path / "trace.json"
+    write_chrome_trace(str(out), ms)
+    assert len(json.load(open(out))["traceEvents"]) == 5
+
+
 def test_golden_trace_512_on_gpu():
     """Published trace of the reference (report.pdf p.15-16 §4.3), on one B200."""
     from mpi_cuda_b200.parallel.fused import FusedSolver

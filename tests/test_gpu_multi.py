@@ -13,6 +13,23 @@ from mpi_cuda_b200.parallel.launch import spawn
 pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 
 
+def _work_skew(rank, world, dims, bc, N, K):
+    """Protocol stress: one rank is artificially late before every step."""
+    import torch
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    dev = torch.device("cuda", rank)
+    p = WaveProblem(N, 2.0, 1e-3, K, bc=bc)
+    s = FusedSolver(p, dims, dev, every=2, use_graph=False, spin_timeout_ms=20000)
+    s.init()
+    for n in range(1, K + 1):
+        if rank == (n % world):
+            torch.cuda._sleep(3_000_000)          # ~1.5 ms of device-side delay on a rotating rank
+        s.step(n, n % 2 == 0)
+    s.barrier()
+    s.check_status()
+    return s.gather_trace()
+
+
 def _work(rank, world, mode, dims, bc, N, K, graph):
     import torch
     from mpi_cuda_b200.parallel.exchange import CudaBlockOps, ExchangeSolver
@@ -44,6 +61,15 @@ def test_two_gpu_trace_equals_one_gpu(mode, dims, bc):
         for a, b in zip(trace, base):
             assert a[2] == b[2]
             assert abs(a[3] - b[3]) <= 1e-12 * b[3]
+
+
+def test_two_gpu_skewed_ranks_still_agree():
+    N, K = (72, 60, 52), 12
+    base, _ = cpu.solve(WaveProblem(N, 2.0, 1e-3, K, bc="ddp"), every=2)
+    out = spawn(_work_skew, 2, ((1, 1, 2), "ddp", N, K), backend="nccl")
+    for trace in out:
+        for a, b in zip(trace, base):
+            assert a[2] == b[2] and abs(a[3] - b[3]) <= 1e-12 * b[3]
 
 
 def test_two_gpu_fused_graph():
