@@ -523,21 +523,30 @@ __global__ void __launch_bounds__(256) box_step_kernel(const __grid_constant__ S
   publish_error(P.err, mx, s2, red);
 }
 
-// K1: analytic layer 0 on every node (ghosts and row padding included)
-__global__ void __launch_bounds__(256) init_kernel(double* u, Geometry g, const double* sx,
-                                                   const double* sy, const double* sz) {
-  const long long rows = (long long)(g.n[1] + 2) * (g.n[2] + 2);
-  const long long total = rows * g.pitch;
-  for (long long id = (long long)blockIdx.x * blockDim.x + threadIdx.x; id < total;
-       id += (long long)gridDim.x * blockDim.x) {
-    const int xe = (int)(id % g.pitch);
-    const long long row = id / g.pitch;
-    const int j = (int)(row % (g.n[1] + 2));
-    const int k = (int)(row / (g.n[1] + 2));
-    const int i = xe - g.xoff;
-    double v = 0.0;
-    if (i >= 0 && i <= g.n[0] + 1) v = sx[i] * (sy[j] * sz[k]);
-    u[id] = v;
+// K1: analytic layer 0 on every node (ghosts and row padding included) of `u`, zeros in
+// `z` (the array that will receive level 1): one warp per row, coalesced stores.
+__global__ void __launch_bounds__(256) init_kernel(double* __restrict__ u, double* __restrict__ z, Geometry g,
+                                                   const double* __restrict__ sx, const double* __restrict__ sy,
+                                                   const double* __restrict__ sz) {
+  const int rows_per_plane = g.n[1] + 2;
+  const long long rows = (long long)rows_per_plane * (g.n[2] + 2);
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const int pitch = (int)g.pitch;
+  for (long long row = warp0; row < rows; row += nwarps) {
+    const int j = (int)(row % rows_per_plane);
+    const int k = (int)(row / rows_per_plane);
+    const double syz = sy[j] * sz[k];
+    double* ur = u + row * g.pitch;
+    double* zr = z + row * g.pitch;
+    for (int xe = lane; xe < pitch; xe += 32) {
+      const int i = xe - g.xoff;
+      double v = 0.0;
+      if (i >= 0 && i <= g.n[0] + 1) v = sx[i] * syz;
+      ur[xe] = v;
+      zr[xe] = 0.0;
+    }
   }
 }
 

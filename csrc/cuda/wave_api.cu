@@ -327,12 +327,11 @@ long long w3d_plan_launches(W3dPlan* plan) { return plan ? plan->launches : 0; }
 int w3d_plan_init(W3dPlan* p, void* stream) {
   if (!p) return fail(W3D_EINVAL, "null plan");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const long long total = (long long)(p->g.n[2] + 2) * p->g.plane;
-  const int blocks = (int)std::min<long long>((total + 255) / 256, (long long)p->num_sms * 16);
-  init_kernel<<<blocks, 256, 0, st>>>(p->d.field[0], p->g, p->d.tab[0], p->d.tab[1], p->d.tab[2]);
+  const long long rows = (long long)(p->g.n[2] + 2) * (p->g.n[1] + 2);
+  const int blocks = (int)std::max<long long>(1, std::min<long long>((rows + 7) / 8, (long long)p->num_sms * 32));
+  init_kernel<<<blocks, 256, 0, st>>>(p->d.field[0], p->d.field[1], p->g, p->d.tab[0], p->d.tab[1], p->d.tab[2]);
   CUDA_TRY(cudaGetLastError());
   ++p->launches;
-  CUDA_TRY(cudaMemsetAsync(p->d.field[1], 0, (size_t)total * sizeof(double), st));
   CUDA_TRY(cudaMemsetAsync(p->d.flags_in, 0, 6 * sizeof(unsigned long long), st));
   CUDA_TRY(cudaMemsetAsync(p->d.status, 0, sizeof(uint32_t), st));
   CUDA_TRY(cudaMemsetAsync(p->d.workspace, 0, kCounterBytes, st));

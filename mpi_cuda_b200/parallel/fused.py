@@ -278,7 +278,8 @@ class StreamingSession:
     ``session.step(n)`` (1) copies that step's time factor cos(a_t t_n) from pinned
     host memory to the device table the kernel reads, (2) launches the fused step,
     (3) copies the step's (max error, sum of squares) back to pinned host memory and
-    waits for it.  This is the end-to-end path a user drives when they want the error
+    waits for it.  ``step_async(n)`` / ``result(n)`` split (3) off so that a caller can
+    keep one step in flight while it consumes the previous step's result.  This is the end-to-end path a user drives when they want the error
     of every step as it happens, the way the reference prints its ``Step`` lines while
     running (report.pdf p.15-16); ``bench.py`` times it as the ``e2e`` number.
     """
@@ -292,6 +293,7 @@ class StreamingSession:
         self.ct_host = torch.from_numpy(solver.ct.copy()).pin_memory()
         self.ct_dev = torch.zeros(p.K + 2, dtype=torch.float64, device=solver.device)
         self.err_host = torch.zeros((p.K + 1, 2), dtype=torch.float64).pin_memory()
+        self._done: Dict[int, torch.cuda.Event] = {}
         solver.plan.set_ct_table(self.ct_dev)
 
     def close(self) -> None:
@@ -310,10 +312,21 @@ class StreamingSession:
     def table_bytes(self) -> int:
         return sum(t.numel() * 8 for t in self.s.tab)
 
-    def step(self, n: int) -> Tuple[float, float]:
+    def step_async(self, n: int) -> None:
+        """Enqueue step n with its host input and the read-back of its result; do not wait."""
         s = self.s
         self.ct_dev[n: n + 1].copy_(self.ct_host[n: n + 1], non_blocking=True)
         s.step(n, True)
         self.err_host[n].copy_(s.trace[n], non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        ev = torch.cuda.Event()
+        ev.record()
+        self._done[n] = ev
+
+    def result(self, n: int) -> Tuple[float, float]:
+        """(max error, sum of squares) of step n on this rank; waits for its read-back only."""
+        self._done.pop(n).synchronize()
         return float(self.err_host[n, 0]), float(self.err_host[n, 1])
+
+    def step(self, n: int) -> Tuple[float, float]:
+        self.step_async(n)
+        return self.result(n)
