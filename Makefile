@@ -33,7 +33,12 @@ $(OUT)/libwave3d_b200.so: $(CU_SRCS) $(CU_HDRS)
 	@mkdir -p $(OUT)
 	$(NVCC) $(NVCCFLAGS) -shared -o $@ $(CU_SRCS) -cudart static
 
-tools: $(BIN)/mpigpu
+tools: $(BIN)/mpigpu $(BIN)/tma_probe3
+
+# bring-up probe that established the 16-byte TMA coordinate rule
+$(BIN)/tma_probe3: csrc/tools/tma_probe3.cu csrc/cuda/ptx.cuh
+	@mkdir -p $(BIN)
+	$(NVCC) -ccbin $(CXX) $(ARCH) -O2 -std=c++17 -Iinclude -o $@ csrc/tools/tma_probe3.cu
 
 $(BIN)/mpigpu: csrc/tools/mpigpu_main.cpp $(OUT)/libwave3d_b200.so
 	@mkdir -p $(BIN)

@@ -92,6 +92,7 @@ struct alignas(64) StepParams {
   const unsigned long long* flags_in;
   unsigned* shell_counter;
   unsigned* status;
+  int debug_skip;                  // diagnostics only (W3D_DEBUG_SKIP): 1 no flag wait, 2 no copy-out, 4 no fence/release
   unsigned long long level;        // level of `cur`
   unsigned long long timeout_ns;
 };
@@ -399,7 +400,7 @@ __device__ void tma_role(const StepParams& P, int x0, int y0, int z0, int z1, in
       tma_prefetch_desc(&P.map_halo);
       tma_prefetch_desc(&P.map_core);
       // ghosts of the current level must have arrived before they are loaded
-      if (mask) wait_peer_flags(P, mask);
+      if (mask && !(P.debug_skip & 1)) wait_peer_flags(P, mask);
     }
     for (int t = 0; t < iters; ++t) {
       if (leader) {
@@ -481,9 +482,9 @@ __device__ void tma_role(const StepParams& P, int x0, int y0, int z0, int z1, in
   }
   if (mask) {
     named_bar_sync(kConsBarrier, Cfg::kConsumers);   // the tile is written (CTA-visible)
-    face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kConsumers);
+    if (!(P.debug_skip & 2)) face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kConsumers);
     named_bar_sync(kConsBarrier, Cfg::kConsumers);   // every consumer's peer stores are issued
-    if (threadIdx.x == 0) face_cta_done(P);
+    if (threadIdx.x == 0 && !(P.debug_skip & 4)) face_cta_done(P);
   }
 }
 

@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -61,7 +62,7 @@ constexpr int kDefaultVariant = 3;   // best of the measured sweep at 512^3 (pro
 
 // ---- workspace layout ---------------------------------------------------------------
 constexpr size_t kCounterBytes = 256;   // tickets [0..7] at 0, face-CTA counter at +64
-constexpr size_t kOrderBytes = (size_t)W3D_MAX_PARTIALS * sizeof(int);   // block -> tile table
+constexpr size_t kOrderBytes = 2 * (size_t)W3D_MAX_PARTIALS * sizeof(int);   // block -> tile tables (even / odd steps)
 constexpr size_t kSlotBytes = 2ull * W3D_MAX_PARTIALS * sizeof(double);
 constexpr size_t kSlotBase = kCounterBytes + kOrderBytes;
 
@@ -292,8 +293,19 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
       (is_face ? face : rest).push_back(w);
     }
     p->n_face_ctas = (int)face.size();
-    face.insert(face.end(), rest.begin(), rest.end());
-    cudaError_t ce = cudaMemcpy(p->order_dev, face.data(), face.size() * sizeof(int), cudaMemcpyHostToDevice);
+    // Even steps sweep the block upwards, odd steps downwards: the planes written last by
+    // step s are the first ones read by step s+1, so whatever the 126 MB L2 still holds of
+    // them is not fetched from HBM again (matters when the local block is a few L2 sizes).
+    std::vector<int> fwd(face), bwd(face.rbegin(), face.rend());
+    fwd.insert(fwd.end(), rest.begin(), rest.end());
+    // (measured: no gain on B200 at 512^3 .. 512x256x128 — profiles/halo_designs.md — so it is
+    // opt-in via W3D_SWEEP_REVERSAL=1 and the default is the same order on every step)
+    const char* rev = std::getenv("W3D_SWEEP_REVERSAL");
+    if (rev && rev[0] == '1') bwd.insert(bwd.end(), rest.rbegin(), rest.rend());
+    else bwd = fwd;
+    cudaError_t ce = cudaMemcpy(p->order_dev, fwd.data(), fwd.size() * sizeof(int), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess)
+      ce = cudaMemcpy(p->order_dev + W3D_MAX_PARTIALS, bwd.data(), bwd.size() * sizeof(int), cudaMemcpyHostToDevice);
     if (ce != cudaSuccess) {
       delete p;
       return fail(W3D_ECUDA, "cudaMemcpy(order table): %s", cudaGetErrorString(ce));
@@ -350,7 +362,7 @@ int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double 
     for (int q = 0; q < P.err.n_bcast; ++q) P.err.bcast[q] = p->d.err_table_peer[q] + off;
   }
   P.tile = p->tile;
-  P.order = p->order_dev;
+  P.order = p->order_dev + ((s & 1) ? W3D_MAX_PARTIALS : 0);
   P.n_face_ctas = p->n_face_ctas;
   P.use_flags = p->any_peer ? 1 : 0;
   const int nxt = (s & 1) ^ 1;
@@ -363,6 +375,7 @@ int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double 
     P.peer[f].plane = q.plane;
     P.peer[f].flag = q.flag;
   }
+  if (const char* dbg = std::getenv("W3D_DEBUG_SKIP")) P.debug_skip = std::atoi(dbg);   // timing diagnostics, wrong results
   P.flags_in = p->d.flags_in;
   P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
   return launch_fused(p, P, p->n_ctas, static_cast<cudaStream_t>(stream));

@@ -256,3 +256,25 @@ def test_golden_trace_512_on_gpu():
     for (n, t, mx, l2), (gn, gt, gmx, gl2) in zip(res.trace, report.GOLDEN_512):
         assert n == gn and abs(mx - gmx) <= 5e-15 and abs(l2 - gl2) <= 1e-6 * gl2
     assert res.lines()[-1][:60] == "Step 20, t = 0.020000, Max Error = 3.960129e-09, L2 Error = 1.40422"[:60]
+
+
+def test_native_mpigpu_executable_matches_python_path():
+    """bin/mpigpu: the Python-free equivalent of `mpirun -np 1 ./mpigpu-1 N tau K 1` (report.pdf p.15)."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "bin", "mpigpu")
+    if not os.path.exists(exe):
+        from mpi_cuda_b200.build import build_tools
+        build_tools()
+    out = subprocess.run([exe, "128", "0.001", "20", "1"], capture_output=True, text=True, check=True).stdout
+    lines = [l for l in out.splitlines() if l.startswith("Step ")]
+    assert out.splitlines()[0] == "Running test with grid size 128^3" and len(lines) == 10
+    base, _ = cpu.solve(WaveProblem(128, 1.0, 1e-3, 20), every=2)
+    for l, b in zip(lines, base):
+        n, t, mx, l2 = report.parse_step(l)
+        assert n == b[0] and abs(mx - b[2]) <= 1e-6 * b[2] and abs(l2 - b[3]) <= 1e-6 * b[3]
+    per = subprocess.run([exe, "96", "0.001", "10", "--bc", "ddp", "--L", "2"], capture_output=True, text=True, check=True).stdout
+    base, _ = cpu.solve(WaveProblem(96, 2.0, 1e-3, 10, bc="ddp"), every=2)
+    got = [report.parse_step(l) for l in per.splitlines() if l.startswith("Step ")]
+    assert len(got) == 5 and abs(got[-1][2] - base[-1][2]) <= 1e-6 * base[-1][2]

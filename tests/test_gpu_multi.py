@@ -89,3 +89,18 @@ def test_four_gpu_blocks(dims):
     out = spawn(_work, 4, ("fused", dims, "dpd", N, K, False), backend="nccl")
     for a, b in zip(out[0], base):
         assert a[2] == b[2]
+
+
+def test_native_mpigpu_two_gpus():
+    """One process, two GPUs, peer access, in-kernel halos: `mpigpu -np 2` == 1 GPU trace."""
+    import os
+    import subprocess
+    from mpi_cuda_b200.utils import report
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "bin", "mpigpu")
+    one = subprocess.run([exe, "160", "0.001", "20"], capture_output=True, text=True, check=True).stdout
+    two = subprocess.run([exe, "-np", "2", "160", "0.001", "20"], capture_output=True, text=True, check=True).stdout
+    a = [l for l in one.splitlines() if l.startswith("Step ")]
+    b = [l for l in two.splitlines() if l.startswith("Step ")]
+    assert len(a) == 10 and a == b          # digit-identical lines, like report.pdf p.15-16
+    assert "and 2 processes" in two.splitlines()[0]

@@ -101,3 +101,32 @@ def test_cli_both_spellings():
     assert abs(f["L"] - PI) < 1e-15 and abs(f["tau"] - 1e-3) < 1e-18
     p, args = parse(["128", "0.001", "20", "4", "--bc", "ddp", "--L", "pi"])
     assert p.N == (128,) * 3 and args.threads == 4 and p.bc == "ddp" and abs(p.L[0] - PI) < 1e-15
+
+
+def test_charts_are_valid_svg():
+    import xml.etree.ElementTree as ET
+    from mpi_cuda_b200.utils.charts import speedup_efficiency_charts
+    # the reference's own headline rows (readme.md:88-100)
+    rows = {"MPI": [(1, 39.21), (10, 6.40), (20, 2.73)], "MPI+CUDA": [(1, 0.752), (2, 0.505)]}
+    sp, ef = speedup_efficiency_charts(rows, 21.98, "512^3")
+    for doc in (sp, ef):
+        root = ET.fromstring(doc)
+        assert root.tag.endswith("svg")
+    assert "MPI+CUDA" in sp and "efficiency" in ef
+
+
+def test_checkpoint_roundtrip_cpu(tmp_path):
+    import torch
+    from mpi_cuda_b200.utils import checkpoint
+    f = [torch.arange(24, dtype=torch.float64).reshape(2, 3, 4), torch.ones(2, 3, 4, dtype=torch.float64)]
+    out = checkpoint.save_state(str(tmp_path / "ck"), 3, 7, f, {"N": (4, 4, 4)})
+    assert out.endswith(".rank3.pt")
+    st = checkpoint.load_state(str(tmp_path / "ck"), 3)
+    assert st["level"] == 7 and torch.equal(st["fields"][0], f[0]) and st["meta"]["N"] == (4, 4, 4)
+
+
+def test_cli_parses_session_flags():
+    p, args = parse(["256", "0.001", "20", "--checkpoint", "/tmp/x", "--checkpoint-at", "10", "--bc", "ddp"])
+    assert args.checkpoint == "/tmp/x" and args.checkpoint_at == 10 and p.bc == "ddp"
+    p, args = parse(["1024", "pi", "0.1", "100", "--decomp", "1x2x4", "--backend", "fused"])
+    assert p.K == 100 and abs(p.tau - 1e-3) < 1e-15 and args.decomp == "1x2x4"
