@@ -114,6 +114,8 @@ def main() -> int:
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--every", type=int, default=2)
+    ap.add_argument("--pair", action="store_true", help="temporal blocking: two steps per pass (1 GPU, Dirichlet)")
+    ap.add_argument("--pair-variant", type=int, default=-1)
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm()
@@ -157,7 +159,7 @@ def main() -> int:
     if args.backend == "fused":
         from mpi_cuda_b200.parallel.fused import FusedSolver, StreamingSession
         s = FusedSolver(p, dims, device, every=args.every, variant=args.variant, zchunk=args.zchunk,
-                        use_graph=not args.no_graph)
+                        use_graph=not args.no_graph, pair=args.pair, pair_variant=args.pair_variant)
         # ---- warm-up: W untimed steps (also loads the module, maps peers) ----
         s.init()
         s._enqueue_steps(1, min(W, K))
@@ -249,7 +251,7 @@ def main() -> int:
         "vs_baseline": glups / pub, "dtype": "fp64", "data": "synthetic (analytic-solution initial layers)",
         "config": {"model": "wave3d leapfrog 7-point", "grid": grid_name, "global_batch": p.n_unknowns,
                    "seq_len": K, "parallelism": f"spatial {dims[0]}x{dims[1]}x{dims[2]}", "backend": args.backend,
-                   "bc": args.bc, "L": list(p.L), "tau": args.tau, "report_every": args.every,
+                   "bc": args.bc, "L": list(p.L), "temporal_blocking": bool(args.pair), "tau": args.tau, "report_every": args.every,
                    "l2_policy": "inputs larger than L2 (2 x %.2f GB fields per GPU vs 126 MB L2), no flush"
                                 % (bytes_per_gpu / 24 * 8 / 1e9),
                    "reps": args.reps, "rep_ms": [round(t, 4) for t in times],

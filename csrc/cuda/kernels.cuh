@@ -369,7 +369,7 @@ __device__ void face_copy_out(const StepParams& P, int mask, int x0, int y0, int
 }
 
 template <class Cfg>
-__device__ void tma_role(const StepParams& P, int x0, int y0, int z0, int z1, int mask, uint8_t* smem,
+__device__ __forceinline__ void tma_role(const StepParams& P, int x0, int y0, int z0, int z1, int mask, uint8_t* smem,
                          double& mx, double& s2) {
   constexpr int TX = Cfg::kTX, RPT = Cfg::kRPT, STAGES = Cfg::kStages, W = Cfg::kW;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
@@ -494,8 +494,9 @@ __device__ void tma_role(const StepParams& P, int x0, int y0, int z0, int z1, in
 template <class Cfg, int MINB>
 __global__ void __launch_bounds__(Cfg::kThreads, MINB)
 fused_step_kernel(const __grid_constant__ StepParams P) {
-  extern __shared__ __align__(128) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  // Indexed directly (no integer round trip) so the compiler keeps the shared address space:
+  // LDS/STS with 32-bit addresses instead of generic LD/ST with 64-bit address arithmetic.
+  extern __shared__ __align__(1024) uint8_t smem[];
   double* red = reinterpret_cast<double*>(smem + 128);
   double mx = 0.0, s2 = 0.0;
   const TileGeom& T = P.tile;

@@ -1,0 +1,320 @@
+// pair_kernel.cuh — temporal blocking: TWO time steps per pass over memory.
+//
+// The single-step kernel moves the algorithmic minimum of 24 B per node and step
+// (read u^n, read u^{n-1}, write u^{n+1}) and runs at the HBM roofline, so the only
+// way to go faster is to move fewer bytes.  This kernel advances two levels in one
+// sweep: it reads u^n and u^{n-1} once and writes u^{n+1} and u^{n+2} once —
+// 32 B per node for two steps = 16 B per node and step.
+//
+// The reference does one halo exchange and one pass per step (report.pdf p.16 §4.4:
+// exchange is an additive per-step phase); temporal blocking is listed as absent in
+// SURVEY.md §2.4, so this has no counterpart there.
+//
+// Structure per CTA (tile TX x TY, chunk of planes [z0,z1)), marching up in z:
+//   * TMA streams, per plane p, a (TX+4)x(TY+4) box of u^n (A) and a (TX+4)x(TY+2)
+//     box of u^{n-1} (B) into the shared-memory ring (same producer/mbarrier scheme
+//     as the single-step kernel);
+//   * level 1 (u^{n+1}) is computed on the tile PLUS a one-node ring around it
+//     ((TX+2)x(TY+2); ring nodes are owned by the first 2(TX+2)+2TY threads), with
+//     the z direction in registers (partial/finish), written to global C for tile
+//     nodes and to a double-buffered shared-memory plane for everyone;
+//   * one consumer barrier per plane, then level 2 (u^{n+2}) is computed on the tile
+//     from that shared plane (x/y neighbours) and registers (z neighbours, and u^n
+//     as the "previous" level), and written to global D;
+//   * both levels can feed the error epilogue.
+// Level-1 values on ring nodes outside the local block are taken as 0 (Dirichlet
+// boundary).  Faces with a neighbour are handled by the host protocol in
+// wave_api.cu (the layer next to such a face is finished by a fix-up launch once the
+// neighbour's level-1 edge has arrived).  The arithmetic is the same
+// w3d_partial/w3d_finish sequence, so results are bit-identical to two single steps.
+#pragma once
+#include "kernels.cuh"
+
+namespace w3d {
+
+template <int TX, int RPT, int RG, int STAGES>
+struct PairCfg {
+  static constexpr int kTX = TX, kRPT = RPT, kRG = RG, kStages = STAGES;
+  static constexpr int kTY = RPT * RG;
+  static constexpr int kWA = TX + 4, kRowsA = kTY + 4;     // u^n box (two ghost layers)
+  static constexpr int kWB = TX + 4, kRowsB = kTY + 2;     // u^{n-1} box (one ghost layer; x padded for alignment)
+  static constexpr int kW1 = TX + 2, kRows1 = kTY + 2;     // level-1 plane kept in shared memory
+  static constexpr int kConsumers = TX * RG;
+  static constexpr int kThreads = kConsumers + 32;
+  static constexpr int kABytes = (kWA * kRowsA * 8 + 127) / 128 * 128;
+  static constexpr int kBBytes = (kWB * kRowsB * 8 + 127) / 128 * 128;
+  static constexpr int kATx = kWA * kRowsA * 8, kBTx = kWB * kRowsB * 8;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kL1Bytes = (kW1 * kRows1 * 8 + 127) / 128 * 128;
+  static constexpr int kBarBytes = 128 + 1024;
+  static constexpr int kSmemBytes = kBarBytes + STAGES * kStageBytes + 2 * kL1Bytes + 128;
+  static constexpr int kRing = 2 * kW1 + 2 * kTY;
+  static_assert(kRing <= kConsumers, "one ring node per consumer thread at most");
+  static_assert(TX % 32 == 0 && kWA <= 256 && kRowsA <= 256, "TMA box limits");
+};
+
+struct alignas(64) PairParams {
+  CUtensorMap map_a;      // (TX+4)x(TY+4)x1 boxes of u^n
+  CUtensorMap map_b;      // (TX+4)x(TY+2)x1 boxes of u^{n-1}
+  Geometry g;
+  double* out1;           // u^{n+1}
+  double* out2;           // u^{n+2}
+  const double* sx;
+  const double* sy;
+  const double* sz;
+  double a1, b1, c1x, c1y, c1z, ct1;   // level n+1 coefficients / time factor
+  double a2, b2, c2x, c2y, c2z, ct2;   // level n+2
+  ErrCtl err1, err2;
+  TileGeom tile;
+  const int* order;
+  // nodes of level 2 that must NOT be produced here: the layer next to a face with a
+  // neighbour (their level-1 ghost is not known yet).  skip_lo/hi[d] = 1 when active.
+  int skip_lo[3], skip_hi[3];
+};
+
+// Consumer side of one CTA.  FULL = every node of the tile is inside the block, is
+// updated by this launch and is not excluded by a skip flag: all per-node predicates
+// fold away and the eight rows of a thread become straight-line code that the compiler
+// can interleave (the dependent FMA chains of one row otherwise expose their latency).
+template <class Cfg, bool FULL>
+__device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* full, uint64_t* empty, uint8_t* stage0,
+                                              double* l1buf, int x0, int y0, int z0, int z1, double& mx1,
+                                              double& s21, double& mx2, double& s22) {
+  constexpr int TX = Cfg::kTX, RPT = Cfg::kRPT, STAGES = Cfg::kStages;
+  constexpr int WA = Cfg::kWA, WB = Cfg::kWB, W1 = Cfg::kW1;
+  const TileGeom& T = P.tile;
+  const Geometry& g = P.g;
+  const int nzc = z1 - z0;
+  const int iters = nzc + 4;
+  const int tid = threadIdx.x;
+  const int cxi = tid % TX;
+  const int r0 = (tid / TX) * RPT;
+  const int gx = x0 + cxi;
+  const bool x_in = gx >= 1 && gx <= g.n[0];                 // inside the local block
+  const bool x_ok = gx >= T.lo[0] && gx < T.hi[0];           // this launch updates it
+  const bool want1 = P.err1.out != nullptr, want2 = P.err2.out != nullptr;
+  double acc1[RPT], zA[RPT], acc2[RPT], zL[RPT], sxy[RPT];
+  bool in1[RPT], st1[RPT], st2[RPT];
+  const double sxv = x_in ? P.sx[gx] : 0.0;
+#pragma unroll
+  for (int r = 0; r < RPT; ++r) {
+    const int gy = y0 + r0 + r;
+    const bool y_in = gy >= 1 && gy <= g.n[1];
+    in1[r] = FULL || (x_in && y_in);                                       // level 1 is meaningful here
+    st1[r] = FULL || (x_ok && gy >= T.lo[1] && gy < T.hi[1]);              // level 1 is stored from here
+    st2[r] = FULL || (st1[r] && !(P.skip_lo[0] && gx == 1) && !(P.skip_hi[0] && gx == g.n[0]) &&
+                      !(P.skip_lo[1] && gy == 1) && !(P.skip_hi[1] && gy == g.n[1]));
+    sxy[r] = in1[r] ? sxv * P.sy[min(max(gy, 0), g.n[1] + 1)] : 0.0;
+    acc1[r] = zA[r] = acc2[r] = zL[r] = 0.0;
+  }
+  // ring node of this thread (level 1 only), in level-1-plane coordinates
+  const bool has_ring = tid < Cfg::kRing;
+  int rcx = 0, rry = 0;
+  if (has_ring) {
+    if (tid < W1) { rcx = tid; rry = 0; }
+    else if (tid < 2 * W1) { rcx = tid - W1; rry = Cfg::kRows1 - 1; }
+    else { const int q = tid - 2 * W1; rcx = (q & 1) ? W1 - 1 : 0; rry = 1 + (q >> 1); }
+  }
+  const int rgx = x0 - 1 + rcx, rgy = y0 - 1 + rry;
+  const bool ring_in = has_ring && rgx >= 1 && rgx <= g.n[0] && rgy >= 1 && rgy <= g.n[1];
+  double racc = 0.0, rzA = 0.0;
+  const int pitch = (int)g.pitch;
+  double* o1 = P.out1 + (long long)(y0 + r0) * g.pitch + g.xoff + gx;
+  double* o2 = P.out2 + (long long)(y0 + r0) * g.pitch + g.xoff + gx;
+  // thread-constant shared-memory offsets (elements)
+  const int offA = (r0 + 1) * WA + cxi + 2;      // A box: tile node (cxi, r0-1)
+  const int offB = (r0 + 1) * WB + cxi + 2;      // B box: tile node (cxi, r0)
+  const int off1 = (r0 + 1) * W1 + cxi + 1;      // level-1 plane: tile node (cxi, r0)
+  const int offRA = (rry + 1) * WA + rcx + 1, offRB = rry * WB + rcx + 1, offR1 = rry * W1 + rcx;
+
+  for (int t = 0; t < iters; ++t) {
+    const int s = t % STAGES;
+    const uint32_t ph = (uint32_t)(t / STAGES) & 1u;
+    const int p = z0 - 2 + t;                 // plane of u^n that has just arrived
+    mbar_wait(full + s, ph);
+    const double* As = reinterpret_cast<const double*>(stage0 + (size_t)s * Cfg::kStageBytes);
+    const double* Bs = reinterpret_cast<const double*>(stage0 + (size_t)s * Cfg::kStageBytes + Cfg::kABytes);
+    double* L1w = l1buf + (size_t)((t + 1) & 1) * (Cfg::kL1Bytes / 8);     // plane p-1 of level 1
+    // ---- level 1 ----
+    double colA[RPT + 2];
+#pragma unroll
+    for (int q = 0; q < RPT + 2; ++q) colA[q] = As[offA + q * WA];
+    const int p1 = p - 1;                                        // level-1 plane completed now
+    const bool p1_live = t >= 2 && p1 >= 1 && p1 <= g.n[2];     // otherwise level 1 is 0 there
+    const bool p1_store = p1 >= z0 && p1 < z1;
+    const bool p_l1 = p >= z0 - 1 && p <= z1;                   // plane p needs a level-1 partial
+    double l1c[RPT];
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) l1c[r] = w3d_finish(acc1[r], colA[r + 1], P.c1z);
+    if (!p1_live) {
+#pragma unroll
+      for (int r = 0; r < RPT; ++r) l1c[r] = 0.0;
+    } else if (!FULL) {
+#pragma unroll
+      for (int r = 0; r < RPT; ++r) l1c[r] = in1[r] ? l1c[r] : 0.0;
+    }
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) L1w[off1 + r * W1] = l1c[r];
+    if (p1_store) {
+      double* o = o1 + (long long)p1 * g.plane;
+#pragma unroll
+      for (int r = 0; r < RPT; ++r)
+        if (FULL || st1[r]) o[r * pitch] = l1c[r];
+      if (want1) {
+        const double szt = P.sz[p1] * P.ct1;
+#pragma unroll
+        for (int r = 0; r < RPT; ++r) {
+          if (FULL || st1[r]) {
+            const double e = w3d_abs_err(l1c[r], sxy[r], szt);
+            mx1 = fmax(mx1, e);
+            s21 = fma(e, e, s21);
+          }
+        }
+      }
+    }
+    double ring_c = 0.0;
+    if (has_ring) {
+      ring_c = As[offRA];
+      double v = w3d_finish(racc, ring_c, P.c1z);
+      if (!(ring_in && p1_live)) v = 0.0;
+      L1w[offR1] = v;
+    }
+    if (p_l1) {
+#pragma unroll
+      for (int r = 0; r < RPT; ++r) {
+        const double xm = As[offA + (r + 1) * WA - 1];
+        const double xp = As[offA + (r + 1) * WA + 1];
+        const double pv = Bs[offB + r * WB];
+        acc1[r] = w3d_partial(colA[r + 1], pv, xm, xp, colA[r], colA[r + 2], zA[r], P.a1, P.b1, P.c1x, P.c1y,
+                              P.c1z);
+      }
+      if (has_ring) {
+        const double* a = As + offRA;
+        racc = w3d_partial(ring_c, Bs[offRB], a[-1], a[1], a[-WA], a[WA], rzA, P.a1, P.b1, P.c1x, P.c1y, P.c1z);
+      }
+    }
+    rzA = ring_c;
+    __syncwarp();
+    if ((tid & 31) == 0) mbar_arrive(empty + s);                 // the stage is free again
+    named_bar_sync(kConsBarrier, Cfg::kConsumers);               // level-1 plane p-1 is complete in smem
+    // ---- level 2 ----
+    const int p2 = p - 2;                                        // level-2 plane completed now
+    if (p2 >= z0 && p2 < z1) {
+      const bool skipz = (P.skip_lo[2] && p2 == 1) || (P.skip_hi[2] && p2 == g.n[2]);
+      double v2[RPT];
+#pragma unroll
+      for (int r = 0; r < RPT; ++r) v2[r] = w3d_finish(acc2[r], l1c[r], P.c2z);
+      if (!skipz) {
+        double* o = o2 + (long long)p2 * g.plane;
+#pragma unroll
+        for (int r = 0; r < RPT; ++r)
+          if (FULL || st2[r]) o[r * pitch] = v2[r];
+        if (want2) {
+          const double szt = P.sz[p2] * P.ct2;
+#pragma unroll
+          for (int r = 0; r < RPT; ++r) {
+            if (FULL || st2[r]) {
+              const double e = w3d_abs_err(v2[r], sxy[r], szt);
+              mx2 = fmax(mx2, e);
+              s22 = fma(e, e, s22);
+            }
+          }
+        }
+      }
+    }
+    if (p1_store) {
+      const double ym0 = L1w[off1 - W1];                 // row above this thread's rows
+      const double ypN = L1w[off1 + RPT * W1];           // row below
+#pragma unroll
+      for (int r = 0; r < RPT; ++r) {
+        const double xm = L1w[off1 + r * W1 - 1];
+        const double xp = L1w[off1 + r * W1 + 1];
+        const double ym = r == 0 ? ym0 : l1c[r - 1];
+        const double yp = r == RPT - 1 ? ypN : l1c[r + 1];
+        acc2[r] = w3d_partial(l1c[r], zA[r], xm, xp, ym, yp, zL[r], P.a2, P.b2, P.c2x, P.c2y, P.c2z);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) {
+      zL[r] = l1c[r];
+      zA[r] = colA[r + 1];
+    }
+  }
+}
+
+template <class Cfg>
+__global__ void __launch_bounds__(Cfg::kThreads, 1) pair_step_kernel(const __grid_constant__ PairParams P) {
+  constexpr int TX = Cfg::kTX, STAGES = Cfg::kStages;
+  // Indexed directly (no integer round trip) so the compiler keeps the shared address space:
+  // LDS/STS with 32-bit addresses instead of generic LD/ST with 64-bit address arithmetic.
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty = full + STAGES;
+  double* red = reinterpret_cast<double*>(smem + 128);
+  uint8_t* stage0 = smem + Cfg::kBarBytes;
+  double* l1buf = reinterpret_cast<double*>(stage0 + (size_t)STAGES * Cfg::kStageBytes);
+
+  const TileGeom& T = P.tile;
+  const Geometry& g = P.g;
+  const int work = P.order ? P.order[blockIdx.x] : (int)blockIdx.x;
+  const int tx = work % T.ntx;
+  const int ty = (work / T.ntx) % T.nty;
+  const int ch = work / (T.ntx * T.nty);
+  const int x0 = T.x0 + tx * TX;
+  const int y0 = T.lo[1] + ty * Cfg::kTY;
+  const int z0 = T.lo[2] + ch * T.zc;
+  const int z1 = min(z0 + T.zc, T.hi[2]);
+  const int nzc = z1 - z0;
+  const int iters = nzc + 4;          // planes z0-2 .. z1+1 of u^n
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, Cfg::kConsumers / 32);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  double mx1 = 0.0, s21 = 0.0, mx2 = 0.0, s22 = 0.0;
+  const int warp = threadIdx.x >> 5;
+  if (warp == Cfg::kConsumers / 32) {
+    // ===== producer warp =====
+    const bool leader = (threadIdx.x & 31) == 0;
+    if (leader) {
+      tma_prefetch_desc(&P.map_a);
+      tma_prefetch_desc(&P.map_b);
+    }
+    for (int t = 0; t < iters; ++t) {
+      if (leader) {
+        const int s = t % STAGES;
+        const uint32_t ph = (uint32_t)(t / STAGES) & 1u;
+        mbar_wait(empty + s, ph ^ 1u);
+        const int p = z0 - 2 + t;
+        const bool need_b = (t >= 1 && t <= nzc + 2);       // planes z0-1 .. z1
+        uint8_t* st = stage0 + (size_t)s * Cfg::kStageBytes;
+        mbar_arrive_expect_tx(full + s, (uint32_t)(Cfg::kATx + (need_b ? Cfg::kBTx : 0)));
+        tma_load_3d(st, &P.map_a, full + s, g.xoff + x0 - 2, y0 - 2, p);
+        if (need_b) tma_load_3d(st + Cfg::kABytes, &P.map_b, full + s, g.xoff + x0 - 2, y0 - 1, p);
+      }
+      __syncwarp();
+    }
+  } else {
+    // every tile node inside the block, updated by this launch, and not next to a skipped face
+    const bool full_tile = x0 >= T.lo[0] && x0 >= 1 && x0 + TX <= T.hi[0] && y0 + Cfg::kTY <= T.hi[1] &&
+                           !(P.skip_lo[0] && x0 <= 1) && !(P.skip_hi[0] && x0 + TX > g.n[0]) &&
+                           !(P.skip_lo[1] && y0 <= 1) && !(P.skip_hi[1] && y0 + Cfg::kTY > g.n[1]);
+    if (full_tile) pair_consumer<Cfg, true>(P, full, empty, stage0, l1buf, x0, y0, z0, z1, mx1, s21, mx2, s22);
+    else pair_consumer<Cfg, false>(P, full, empty, stage0, l1buf, x0, y0, z0, z1, mx1, s21, mx2, s22);
+  }
+  if (P.err1.out != nullptr) {
+    __syncthreads();
+    publish_error(P.err1, mx1, s21, red);
+  }
+  if (P.err2.out != nullptr) {
+    __syncthreads();
+    publish_error(P.err2, mx2, s22, red);
+  }
+}
+
+}  // namespace w3d

@@ -5,6 +5,7 @@
 // there, every step staged halos D2H -> MPI_Sendrecv -> H2D; here
 // a step is one kernel launch and nothing crosses the host.
 #include "kernels.cuh"
+#include "pair_kernel.cuh"
 
 #include <algorithm>
 #include <cstdarg>
@@ -58,6 +59,28 @@ const Variant kVariants[] = {
     {Cfg5::kTX, Cfg5::kTY, Cfg5::kThreads, Cfg5::kSmemBytes, 2, fused_step_kernel<Cfg5, 2>, "64x16x6st"},
 };
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
+
+// ---- temporal-blocking (two steps per pass) variants ----
+using PCfg0 = PairCfg<64, 8, 4, 4>;    // 64 x 32 tile, 288 threads, 4-stage ring (~188 KB)
+using PCfg1 = PairCfg<64, 8, 4, 3>;    // 3-stage ring (~150 KB)
+using PCfg2 = PairCfg<128, 8, 4, 2>;   // 128 x 32 tile, 544 threads, 2-stage ring (~215 KB)
+using PCfg3 = PairCfg<64, 4, 8, 4>;    // 64 x 32 tile, 4 rows per thread: 544 threads (16 consumer warps)
+using PCfg4 = PairCfg<64, 4, 8, 3>;
+using PCfg5 = PairCfg<64, 2, 15, 4>;   // 64 x 30 tile, 2 rows per thread: 992 threads (30 consumer warps)
+struct PairVariant {
+  int tx, ty, threads, smem;
+  void (*kernel)(const PairParams);
+  const char* name;
+};
+const PairVariant kPairVariants[] = {
+    {PCfg0::kTX, PCfg0::kTY, PCfg0::kThreads, PCfg0::kSmemBytes, pair_step_kernel<PCfg0>, "pair 64x32x4st"},
+    {PCfg1::kTX, PCfg1::kTY, PCfg1::kThreads, PCfg1::kSmemBytes, pair_step_kernel<PCfg1>, "pair 64x32x3st"},
+    {PCfg2::kTX, PCfg2::kTY, PCfg2::kThreads, PCfg2::kSmemBytes, pair_step_kernel<PCfg2>, "pair 128x32x2st"},
+    {PCfg3::kTX, PCfg3::kTY, PCfg3::kThreads, PCfg3::kSmemBytes, pair_step_kernel<PCfg3>, "pair 64x32x4st rpt4"},
+    {PCfg4::kTX, PCfg4::kTY, PCfg4::kThreads, PCfg4::kSmemBytes, pair_step_kernel<PCfg4>, "pair 64x32x3st rpt4"},
+    {PCfg5::kTX, PCfg5::kTY, PCfg5::kThreads, PCfg5::kSmemBytes, pair_step_kernel<PCfg5>, "pair 64x30x4st rpt2"},
+};
+constexpr int kNumPairVariants = sizeof(kPairVariants) / sizeof(kPairVariants[0]);
 constexpr int kDefaultVariant = 3;   // best of the measured sweep at 512^3 (profiles/variant_sweep.md)
 
 // ---- workspace layout ---------------------------------------------------------------
@@ -99,6 +122,13 @@ struct W3dPlan {
   int* order_dev;                  // lives in the workspace
   bool any_peer;
   const double* ct_table;          // optional device table of cos(a_t t_n), host-fed
+  // temporal blocking: four arrays (0,1 = desc.field, 2,3 = aux), two TMA maps each
+  double* arr[4];
+  CUtensorMap pmap_a[4], pmap_b[4];
+  int pair_variant;
+  TileGeom ptile;
+  int pn_ctas;
+  bool pair_ready;
   long long launches;
   char text[768];
 };
@@ -260,6 +290,7 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
     p->num_sms = sms;
   }
   p->maps_ok = false;
+  p->pair_ready = false;
   p->launches = 0;
   p->ct_table = nullptr;
   p->any_peer = false;
@@ -428,6 +459,100 @@ int w3d_step_box(W3dPlan* p, int s, double a, double b, double cscale, double ct
   }
   const int blocks = (int)std::min<long long>((nodes + 255) / 256, (long long)W3D_MAX_PARTIALS);
   box_step_kernel<<<blocks, 256, 0, st>>>(P);
+  CUDA_TRY(cudaGetLastError());
+  ++p->launches;
+  return W3D_OK;
+}
+
+int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, int pair_variant, int zchunk) {
+  if (!p || !aux0 || !aux1) return fail(W3D_EINVAL, "null argument");
+  if ((reinterpret_cast<uintptr_t>(aux0) | reinterpret_cast<uintptr_t>(aux1)) & 15)
+    return fail(W3D_EINVAL, "aux arrays must be 16-byte aligned");
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled is not available from the driver");
+  p->pair_variant = pair_variant >= 0 && pair_variant < kNumPairVariants ? pair_variant : 0;
+  const PairVariant& v = kPairVariants[p->pair_variant];
+  p->arr[0] = p->d.field[0]; p->arr[1] = p->d.field[1]; p->arr[2] = aux0; p->arr[3] = aux1;
+  const cuuint64_t dims[3] = {(cuuint64_t)p->g.pitch, (cuuint64_t)(p->g.n[1] + 2), (cuuint64_t)(p->g.n[2] + 2)};
+  const cuuint64_t strides[2] = {(cuuint64_t)p->g.pitch * 8, (cuuint64_t)p->g.plane * 8};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const cuuint32_t ab[3] = {(cuuint32_t)(v.tx + 4), (cuuint32_t)(v.ty + 4), 1};
+  const cuuint32_t bb[3] = {(cuuint32_t)(v.tx + 4), (cuuint32_t)(v.ty + 2), 1};
+  for (int f = 0; f < 4; ++f) {
+    CUresult r = enc(&p->pmap_a[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, p->arr[f], dims, strides, ab, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled(pair A) failed: %d", (int)r);
+    r = enc(&p->pmap_b[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, p->arr[f], dims, strides, bb, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled(pair B) failed: %d", (int)r);
+  }
+  CUDA_TRY(cudaFuncSetAttribute(v.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v.smem));
+  // tile geometry over the whole block (one CTA per SM; chunk cost includes 4 extra planes)
+  TileGeom& t = p->ptile;
+  for (int d = 0; d < 3; ++d) { t.lo[d] = 1; t.hi[d] = p->g.n[d] + 1; }
+  t.x0 = 1 - ((p->g.xoff + 1) & 1);
+  t.ntx = (t.hi[0] - t.x0 + v.tx - 1) / v.tx;
+  t.nty = (p->g.n[1] + v.ty - 1) / v.ty;
+  const int ez = p->g.n[2];
+  const long long tiles = (long long)t.ntx * t.nty;
+  if (zchunk > 0) {
+    t.zc = std::min(zchunk, ez);
+  } else {
+    double best = 1e300;
+    int best_c = 1;
+    for (int c = 1; c <= std::max(1, ez / 16); ++c) {
+      const int zc = (ez + c - 1) / c;
+      const long long ctas = tiles * ((ez + zc - 1) / zc);
+      if (ctas > W3D_MAX_PARTIALS) break;
+      const long long waves = (ctas + p->num_sms - 1) / p->num_sms;
+      const double cost = (double)waves * (zc + 4.0 * 0.45 + 2.0);
+      if (cost < best - 1e-9) { best = cost; best_c = c; }
+    }
+    t.zc = (ez + best_c - 1) / best_c;
+  }
+  t.nchunks = (ez + t.zc - 1) / t.zc;
+  p->pn_ctas = t.ntx * t.nty * t.nchunks;
+  if (p->pn_ctas > W3D_MAX_PARTIALS) return fail(W3D_EINVAL, "pair kernel needs %d CTAs, limit %d", p->pn_ctas, W3D_MAX_PARTIALS);
+  p->pair_ready = true;
+  const size_t used = std::strlen(p->text);
+  snprintf(p->text + used, sizeof(p->text) - used, " || %s (%d thr, %d B smem): tiles %dx%d zc %d chunks %d -> %d CTAs",
+           v.name, v.threads, v.smem, t.ntx, t.nty, t.zc, t.nchunks, p->pn_ctas);
+  return W3D_OK;
+}
+
+int w3d_step_pair(W3dPlan* p, int cur, int prev, int out1, int out2, double a1, double b1, double cscale1,
+                  double ct1, double a2, double b2, double cscale2, double ct2, double* err1, double* err2,
+                  void* stream) {
+  if (!p || !p->pair_ready) return fail(W3D_EINVAL, "w3d_plan_enable_pairs has not been called");
+  const int idx[4] = {cur, prev, out1, out2};
+  for (int i = 0; i < 4; ++i) {
+    if (idx[i] < 0 || idx[i] > 3) return fail(W3D_EINVAL, "array index out of range");
+    for (int j = 0; j < i; ++j)
+      if (idx[i] == idx[j]) return fail(W3D_EINVAL, "the four arrays of a pair step must be distinct");
+  }
+  const PairVariant& v = kPairVariants[p->pair_variant];
+  PairParams P;
+  std::memset(&P, 0, sizeof(P));
+  P.map_a = p->pmap_a[cur];
+  P.map_b = p->pmap_b[prev];
+  P.g = p->g;
+  P.out1 = p->arr[out1];
+  P.out2 = p->arr[out2];
+  P.sx = p->d.tab[0]; P.sy = p->d.tab[1]; P.sz = p->d.tab[2];
+  P.a1 = a1; P.b1 = b1; P.c1x = cscale1 * p->d.coef[0]; P.c1y = cscale1 * p->d.coef[1]; P.c1z = cscale1 * p->d.coef[2];
+  P.a2 = a2; P.b2 = b2; P.c2x = cscale2 * p->d.coef[0]; P.c2y = cscale2 * p->d.coef[1]; P.c2z = cscale2 * p->d.coef[2];
+  P.ct1 = ct1; P.ct2 = ct2;
+  P.err1 = err_ctl(p, 0, err1);
+  P.err2 = err_ctl(p, 1, err2);
+  P.tile = p->ptile;
+  P.order = nullptr;
+  for (int d = 0; d < 3; ++d) {
+    P.skip_lo[d] = p->d.peer[d * 2].active ? 1 : 0;
+    P.skip_hi[d] = p->d.peer[d * 2 + 1].active ? 1 : 0;
+  }
+  v.kernel<<<p->pn_ctas, v.threads, v.smem, static_cast<cudaStream_t>(stream)>>>(P);
   CUDA_TRY(cudaGetLastError());
   ++p->launches;
   return W3D_OK;

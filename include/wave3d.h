@@ -121,6 +121,19 @@ int w3d_step_tma(W3dPlan* plan, int s, double a, double b, double cscale, double
 int w3d_step_box(W3dPlan* plan, int s, double a, double b, double cscale, double ct,
                  const int32_t lo[3], const int32_t hi[3], double* err_out, int slot, void* stream);
 
+/* Temporal blocking: two time steps in one pass over memory (16 B per node and step instead
+ * of 24; no counterpart in the reference, which does one pass per step).  Needs two more
+ * arrays of the same layout; the four arrays are addressed by index: 0,1 = desc.field[0..1],
+ * 2,3 = aux0, aux1.  w3d_step_pair reads level n from `cur` and level n-1 from `prev` and
+ * writes level n+1 to `out1` and level n+2 to `out2` (all four distinct).  (a,b,cscale,ct)
+ * are given per produced level.  Nodes next to a face that has a neighbour are left out of
+ * `out2` (their level-n+1 ghost is not known inside the pass); the caller finishes them
+ * with w3d_step_box after the exchange of level n+1. */
+int w3d_plan_enable_pairs(W3dPlan* plan, double* aux0, double* aux1, int pair_variant, int zchunk);
+int w3d_step_pair(W3dPlan* plan, int cur, int prev, int out1, int out2, double a1, double b1, double cscale1,
+                  double ct1, double a2, double b2, double cscale2, double ct2, double* err1, double* err2,
+                  void* stream);
+
 /* NCCL-baseline helpers (K5): contiguous face buffers of the unknowns of the two
  * other axes, fastest index first.  ghost=0 packs/unpacks the edge layer of
  * unknowns, ghost=1 the ghost layer. */

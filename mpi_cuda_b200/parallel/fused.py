@@ -44,7 +44,7 @@ def _field_bytes(n: Sequence[int]) -> int:
 class FusedSolver:
     def __init__(self, p: WaveProblem, dims: Sequence[int] = (1, 1, 1), device: Optional[torch.device] = None,
                  group=None, every: int = 2, variant: int = -1, zchunk: int = 0, use_graph: bool = True,
-                 spin_timeout_ms: int = 0):
+                 spin_timeout_ms: int = 0, pair: bool = False, pair_variant: int = -1):
         self.p, self.dims, self.every = p, tuple(int(d) for d in dims), every
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -110,6 +110,14 @@ class FusedSolver:
         self.ct = time_table(p)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.kernel_launches = 0
+        # ---- temporal blocking (two steps per pass): two more arrays ----
+        self.pair = bool(pair)
+        self.final_index = None          # array index (0..3) holding level K after run_steps in pair mode
+        if self.pair:
+            if self.world > 1 or any(p.periodic):
+                raise NotImplementedError("pair mode currently supports one GPU with Dirichlet boundaries")
+            self.aux = [torch.zeros(shape, dtype=torch.float64, device=self.device) for _ in range(2)]
+            self.plan.enable_pairs(self.aux[0], self.aux[1], pair_variant, zchunk)
 
     # ------------------------------------------------------------------
     def describe(self) -> str:
@@ -136,8 +144,33 @@ class FusedSolver:
         self.kernel_launches += 1
 
     def _enqueue_steps(self, first: int, last: int) -> None:
+        if self.pair and first == 1:
+            self._enqueue_pairs(last)
+            return
         for n in range(first, last + 1):
             self.step(n, n % self.every == 0)
+
+    def _enqueue_pairs(self, last: int) -> None:
+        """Levels 1..last with two steps per launch (plus one single step if `last` is odd).
+
+        Array roles rotate over the four arrays: (cur, prev) -> (out1, out2) = (0,1)->(2,3),
+        (3,2)->(0,1), (1,0)->(2,3), ..."""
+        n = 0
+        cur, prev = 0, 1
+        if last % 2 == 1:                 # odd count: the Taylor step goes alone, in place
+            self.step(1, 1 % self.every == 0)
+            n, cur, prev = 1, 1, 0
+        while n < last:
+            out1, out2 = (2, 3) if cur in (0, 1) else (0, 1)
+            l1 = step_coeffs(n + 1) + (float(self.ct[n + 1]),)
+            l2 = step_coeffs(n + 2) + (float(self.ct[n + 2]),)
+            e1 = self.trace[n + 1] if (n + 1) % self.every == 0 else None
+            e2 = self.trace[n + 2] if (n + 2) % self.every == 0 else None
+            self.plan.step_pair(cur, prev, out1, out2, l1, l2, e1, e2)
+            self.kernel_launches += 1
+            n += 2
+            cur, prev = out2, out1
+        self.final_index = cur
 
     def capture(self) -> None:
         """Capture steps 1..K into one CUDA graph (launch-bound at small blocks)."""
@@ -158,7 +191,7 @@ class FusedSolver:
         """Enqueue all K steps on the current stream (graph replay if captured)."""
         if self.use_graph and self.graph is not None:
             self.graph.replay()
-            self.kernel_launches += self.p.K
+            self.kernel_launches += (self.p.K + 1) // 2 if self.pair else self.p.K
         else:
             self._enqueue_steps(1, self.p.K)
 
@@ -219,6 +252,14 @@ class FusedSolver:
     def field(self, parity: int) -> torch.Tensor:
         xo = cuda.XOFF + 1
         return self.f[parity][1:-1, 1:-1, xo: xo + self.blk.n[0]].contiguous()
+
+    def final_field(self) -> torch.Tensor:
+        """Owned unknowns of the last level computed by run_steps (any mode)."""
+        if self.pair and self.final_index is not None:
+            arr = (self.f + self.aux)[self.final_index]
+            xo = cuda.XOFF + 1
+            return arr[1:-1, 1:-1, xo: xo + self.blk.n[0]].contiguous()
+        return self.field(self.p.K & 1)
 
     # -- tracing ---------------------------------------------------------------
     def profile_steps(self) -> List[float]:

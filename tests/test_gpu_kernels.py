@@ -278,3 +278,29 @@ def test_native_mpigpu_executable_matches_python_path():
     base, _ = cpu.solve(WaveProblem(96, 2.0, 1e-3, 10, bc="ddp"), every=2)
     got = [report.parse_step(l) for l in per.splitlines() if l.startswith("Step ")]
     assert len(got) == 5 and abs(got[-1][2] - base[-1][2]) <= 1e-6 * base[-1][2]
+
+
+@pytest.mark.parametrize("pair_variant", [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize("N,K", [((70, 45, 37), 6), ((130, 66, 50), 7), ((257, 40, 23), 4)])
+def test_pair_kernel_bit_exact_vs_cpu(N, K, pair_variant):
+    """Temporal blocking (two steps per pass) must give exactly the fields of K single steps."""
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem(N, 1.0, 1e-3, K)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=True, pair_variant=pair_variant)
+    res = s.run()
+    ref, tab, b = _cpu_fields(p, K)
+    got = s.final_field().cpu().numpy()
+    assert np.array_equal(got, ref[K]), f"max diff {np.max(np.abs(got - ref[K]))}"
+    base, _ = cpu.solve(p, every=1)
+    assert len(res.trace) == K
+    for a, c in zip(res.trace, base):
+        assert a[2] == c[2] and abs(a[3] - c[3]) <= 1e-12 * c[3]
+
+
+def test_pair_kernel_golden_trace_and_graph():
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem(512, 1.0, 1e-3, 20)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=True, pair=True)
+    res = s.run()
+    for (n, t, mx, l2), (gn, gt, gmx, gl2) in zip(res.trace, report.GOLDEN_512):
+        assert n == gn and abs(mx - gmx) <= 5e-15 and abs(l2 - gl2) <= 1e-6 * gl2
