@@ -46,7 +46,8 @@ struct PairCfg {
   static constexpr int kATx = kWA * kRowsA * 8, kBTx = kWB * kRowsB * 8;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kL1Bytes = (kW1 * kRows1 * 8 + 127) / 128 * 128;
-  static constexpr int kBarBytes = 128 + 1024;
+  static constexpr int kSzEntries = 640;                   // staged slice of the z table (chunk + 4 planes)
+  static constexpr int kBarBytes = 128 + 1024 + kSzEntries * 8;
   static constexpr int kSmemBytes = kBarBytes + STAGES * kStageBytes + 2 * kL1Bytes + 128;
   static constexpr int kRing = 2 * kW1 + 2 * kTY;
   static_assert(kRing <= kConsumers, "one ring node per consumer thread at most");
@@ -76,10 +77,10 @@ struct alignas(64) PairParams {
 // updated by this launch and is not excluded by a skip flag: all per-node predicates
 // fold away and the eight rows of a thread become straight-line code that the compiler
 // can interleave (the dependent FMA chains of one row otherwise expose their latency).
-template <class Cfg, bool FULL>
+template <class Cfg, bool FULL, bool XFULL>
 __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* full, uint64_t* empty, uint8_t* stage0,
-                                              double* l1buf, int x0, int y0, int z0, int z1, double& mx1,
-                                              double& s21, double& mx2, double& s22) {
+                                              double* l1buf, const double* s_sz, int x0, int y0, int z0, int z1,
+                                              double& mx1, double& s21, double& mx2, double& s22) {
   constexpr int TX = Cfg::kTX, RPT = Cfg::kRPT, STAGES = Cfg::kStages;
   constexpr int WA = Cfg::kWA, WB = Cfg::kWB, W1 = Cfg::kW1;
   const TileGeom& T = P.tile;
@@ -100,10 +101,13 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
   for (int r = 0; r < RPT; ++r) {
     const int gy = y0 + r0 + r;
     const bool y_in = gy >= 1 && gy <= g.n[1];
-    in1[r] = FULL || (x_in && y_in);                                       // level 1 is meaningful here
-    st1[r] = FULL || (x_ok && gy >= T.lo[1] && gy < T.hi[1]);              // level 1 is stored from here
-    st2[r] = FULL || (st1[r] && !(P.skip_lo[0] && gx == 1) && !(P.skip_hi[0] && gx == g.n[0]) &&
-                      !(P.skip_lo[1] && gy == 1) && !(P.skip_hi[1] && gy == g.n[1]));
+    // FULL: the tile is complete in y and free of skipped rows, so only the thread-constant
+    // x conditions remain (a partial last tile in x just switches whole columns off)
+    // XFULL additionally: complete in x and free of skipped columns -> no predicate at all
+    in1[r] = (XFULL || x_in) && (FULL || y_in);                             // level 1 is meaningful here
+    st1[r] = (XFULL || x_ok) && (FULL || (gy >= T.lo[1] && gy < T.hi[1]));  // level 1 is stored from here
+    st2[r] = st1[r] && (XFULL || (!(P.skip_lo[0] && gx == 1) && !(P.skip_hi[0] && gx == g.n[0]))) &&
+             (FULL || (!(P.skip_lo[1] && gy == 1) && !(P.skip_hi[1] && gy == g.n[1])));
     sxy[r] = in1[r] ? sxv * P.sy[min(max(gy, 0), g.n[1] + 1)] : 0.0;
     acc1[r] = zA[r] = acc2[r] = zL[r] = 0.0;
   }
@@ -149,7 +153,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
     if (!p1_live) {
 #pragma unroll
       for (int r = 0; r < RPT; ++r) l1c[r] = 0.0;
-    } else if (!FULL) {
+    } else if (!(FULL && XFULL)) {
 #pragma unroll
       for (int r = 0; r < RPT; ++r) l1c[r] = in1[r] ? l1c[r] : 0.0;
     }
@@ -159,12 +163,12 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
       double* o = o1 + (long long)p1 * g.plane;
 #pragma unroll
       for (int r = 0; r < RPT; ++r)
-        if (FULL || st1[r]) o[r * pitch] = l1c[r];
+        if (st1[r]) o[r * pitch] = l1c[r];
       if (want1) {
-        const double szt = P.sz[p1] * P.ct1;
+        const double szt = s_sz[t - 1] * P.ct1;      // s_sz[i] = sz[z0 - 2 + i]
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
-          if (FULL || st1[r]) {
+          if (st1[r]) {
             const double e = w3d_abs_err(l1c[r], sxy[r], szt);
             mx1 = fmax(mx1, e);
             s21 = fma(e, e, s21);
@@ -208,12 +212,12 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
         double* o = o2 + (long long)p2 * g.plane;
 #pragma unroll
         for (int r = 0; r < RPT; ++r)
-          if (FULL || st2[r]) o[r * pitch] = v2[r];
+          if (st2[r]) o[r * pitch] = v2[r];
         if (want2) {
-          const double szt = P.sz[p2] * P.ct2;
+          const double szt = s_sz[t - 2] * P.ct2;
 #pragma unroll
           for (int r = 0; r < RPT; ++r) {
-            if (FULL || st2[r]) {
+            if (st2[r]) {
               const double e = w3d_abs_err(v2[r], sxy[r], szt);
               mx2 = fmax(mx2, e);
               s22 = fma(e, e, s22);
@@ -251,6 +255,7 @@ __global__ void __launch_bounds__(Cfg::kThreads, 1) pair_step_kernel(const __gri
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
   uint64_t* empty = full + STAGES;
   double* red = reinterpret_cast<double*>(smem + 128);
+  double* s_sz = reinterpret_cast<double*>(smem + 128 + 1024);
   uint8_t* stage0 = smem + Cfg::kBarBytes;
   double* l1buf = reinterpret_cast<double*>(stage0 + (size_t)STAGES * Cfg::kStageBytes);
 
@@ -274,6 +279,8 @@ __global__ void __launch_bounds__(Cfg::kThreads, 1) pair_step_kernel(const __gri
     }
     fence_barrier_init();
   }
+  // z slice of the analytic table for the error epilogue: a global load per plane inside the
+  // loop exposed its full latency to every consumer warp (ncu: top long-scoreboard stall)
   __syncthreads();
 
   double mx1 = 0.0, s21 = 0.0, mx2 = 0.0, s22 = 0.0;
@@ -300,12 +307,24 @@ __global__ void __launch_bounds__(Cfg::kThreads, 1) pair_step_kernel(const __gri
       __syncwarp();
     }
   } else {
+    // staged by the consumers only, after the CTA barrier, so the producer's first TMA loads
+    // are already in flight meanwhile
+    for (int i = threadIdx.x; i < iters && i < Cfg::kSzEntries; i += Cfg::kConsumers) {
+      const int k = z0 - 2 + i;
+      s_sz[i] = (k >= 0 && k <= g.n[2] + 1) ? P.sz[k] : 0.0;
+    }
+    named_bar_sync(kConsBarrier, Cfg::kConsumers);
     // every tile node inside the block, updated by this launch, and not next to a skipped face
-    const bool full_tile = x0 >= T.lo[0] && x0 >= 1 && x0 + TX <= T.hi[0] && y0 + Cfg::kTY <= T.hi[1] &&
-                           !(P.skip_lo[0] && x0 <= 1) && !(P.skip_hi[0] && x0 + TX > g.n[0]) &&
-                           !(P.skip_lo[1] && y0 <= 1) && !(P.skip_hi[1] && y0 + Cfg::kTY > g.n[1]);
-    if (full_tile) pair_consumer<Cfg, true>(P, full, empty, stage0, l1buf, x0, y0, z0, z1, mx1, s21, mx2, s22);
-    else pair_consumer<Cfg, false>(P, full, empty, stage0, l1buf, x0, y0, z0, z1, mx1, s21, mx2, s22);
+    const bool full_tile = y0 + Cfg::kTY <= T.hi[1] && !(P.skip_lo[1] && y0 <= 1) &&
+                           !(P.skip_hi[1] && y0 + Cfg::kTY > g.n[1]);
+    const bool xfull = x0 >= T.lo[0] && x0 >= 1 && x0 + TX <= T.hi[0] && !(P.skip_lo[0] && x0 <= 1) &&
+                       !(P.skip_hi[0] && x0 + TX > g.n[0]);
+    if (full_tile && xfull)
+      pair_consumer<Cfg, true, true>(P, full, empty, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
+    else if (full_tile)
+      pair_consumer<Cfg, true, false>(P, full, empty, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
+    else
+      pair_consumer<Cfg, false, false>(P, full, empty, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
   }
   if (P.err1.out != nullptr) {
     __syncthreads();

@@ -498,12 +498,13 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, int pair_varia
   const int ez = p->g.n[2];
   const long long tiles = (long long)t.ntx * t.nty;
   if (zchunk > 0) {
-    t.zc = std::min(zchunk, ez);
+    t.zc = std::min(std::min(zchunk, ez), 636);
   } else {
     double best = 1e300;
-    int best_c = 1;
+    int best_c = std::max(1, (ez + 635) / 636);
     for (int c = 1; c <= std::max(1, ez / 16); ++c) {
       const int zc = (ez + c - 1) / c;
+      if (zc + 4 > 640) continue;                 // the kernel stages zc+4 table entries in shared memory
       const long long ctas = tiles * ((ez + zc - 1) / zc);
       if (ctas > W3D_MAX_PARTIALS) break;
       const long long waves = (ctas + p->num_sms - 1) / p->num_sms;
