@@ -75,6 +75,7 @@ struct alignas(64) StepParams {
   Geometry g;
   const double* cur;
   double* nxt;
+  const double* prev_sep;  // previous level when it is NOT stored in `nxt` (fix-up pass of the pair scheme)
   const double* sx;
   const double* sy;
   const double* sz;
@@ -214,7 +215,7 @@ __device__ void shell_compute(const StepParams& P, long long first, long long st
         yp[u] = c[g.pitch];
         zm[u] = c[-g.plane];
         zp[u] = c[g.plane];
-        pv[u] = P.nxt[off[u]];
+        pv[u] = P.prev_sep ? P.prev_sep[off[u]] : P.nxt[off[u]];
       }
     }
 #pragma unroll
@@ -255,7 +256,8 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 // Spin (bounded) until the neighbours named in `mask` have delivered level P.level.
-__device__ void wait_peer_flags(const StepParams& P, int mask) {
+template <class PT>
+__device__ __noinline__ void wait_peer_flags(const PT& P, int mask) {
   for (int f = 0; f < 6; ++f) {
     if (!(mask & (1 << f))) continue;
     const unsigned long long t0 = globaltimer_ns();
@@ -271,7 +273,8 @@ __device__ void wait_peer_flags(const StepParams& P, int mask) {
 
 // Called by ONE thread of a face CTA after all of the CTA's stores are ordered before
 // it (CTA-scope barrier).  The last face CTA publishes level+1 to every neighbour.
-__device__ void face_cta_done(const StepParams& P) {
+template <class PT>
+__device__ __noinline__ void face_cta_done(const PT& P) {
   __threadfence_system();
   const unsigned done = atomicAdd(P.shell_counter, 1u);
   if (done == (unsigned)P.n_face_ctas - 1u) {
@@ -308,7 +311,8 @@ struct TileCfg {
 };
 
 // faces of the block that the tile (tx,ty,ch) touches and that have a neighbour: bit axis*2+side
-__device__ __forceinline__ int tile_face_mask(const StepParams& P, int x0, int y0, int z0, int z1, int tx_w,
+template <class PT>
+__device__ __forceinline__ int tile_face_mask(const PT& P, int x0, int y0, int z0, int z1, int tx_w,
                                               int ty_w) {
   if (!P.use_flags) return 0;
   int m = 0;
@@ -325,7 +329,8 @@ __device__ __forceinline__ int tile_face_mask(const StepParams& P, int x0, int y
 // layers out of the local array (just written: L2 hits) into the neighbours' ghost
 // layers.  Keeping this out of the streaming loop leaves that loop identical for face
 // and interior CTAs.  tid/nthreads: consumer thread index and count.
-__device__ void face_copy_out(const StepParams& P, int mask, int x0, int y0, int z0, int z1, int tx_w, int ty_w,
+template <class PT>
+__device__ __noinline__ void face_copy_out(const PT& P, int mask, int x0, int y0, int z0, int z1, int tx_w, int ty_w,
                               int tid, int nthreads) {
   const Geometry& g = P.g;
   const TileGeom& T = P.tile;
@@ -524,6 +529,31 @@ __global__ void __launch_bounds__(256) box_step_kernel(const __grid_constant__ S
   double mx = 0.0, s2 = 0.0;
   shell_compute(P, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x,
                 P.boxes.prefix[P.boxes.nboxes], false, mx, s2);
+  publish_error(P.err, mx, s2, red);
+}
+
+// Fix-up pass of the two-step scheme: the layer next to every face with a neighbour gets
+// its second level once the neighbour's first-level edge has arrived.  One thread per node
+// over the shell boxes; acquires the flags for P.level, stores locally and into the
+// neighbours' ghost layers, and the last CTA releases P.level + 1.
+__global__ void __launch_bounds__(256) fixup_kernel(const __grid_constant__ StepParams P) {
+  __shared__ double red[66];
+  double mx = 0.0, s2 = 0.0;
+  if (P.use_flags) {
+    if (threadIdx.x == 0) {
+      int mask = 0;
+      for (int f = 0; f < 6; ++f)
+        if (P.peer[f].active) mask |= 1 << f;
+      wait_peer_flags(P, mask);
+    }
+    __syncthreads();
+  }
+  shell_compute(P, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x,
+                P.boxes.prefix[P.boxes.nboxes], P.use_flags != 0, mx, s2);
+  if (P.use_flags) {
+    __syncthreads();
+    if (threadIdx.x == 0) face_cta_done(P);
+  }
   publish_error(P.err, mx, s2, red);
 }
 

@@ -40,7 +40,10 @@ struct PairCfg {
   static constexpr int kWB = TX + 4, kRowsB = kTY + 2;     // u^{n-1} box (one ghost layer; x padded for alignment)
   static constexpr int kW1 = TX + 2, kRows1 = kTY + 2;     // level-1 plane kept in shared memory
   static constexpr int kConsumers = TX * RG;
-  static constexpr int kThreads = kConsumers + 32;
+  // no separate producer warp: thread 0 issues the TMA loads from inside the consumer loop.
+  // 256 threads = 8 warps lifts the per-thread register ceiling from 168 (288 threads are
+  // allocated as 12 warps) to 255, which this kernel needs to stay spill-free.
+  static constexpr int kThreads = kConsumers;
   static constexpr int kABytes = (kWA * kRowsA * 8 + 127) / 128 * 128;
   static constexpr int kBBytes = (kWB * kRowsB * 8 + 127) / 128 * 128;
   static constexpr int kATx = kWA * kRowsA * 8, kBTx = kWB * kRowsB * 8;
@@ -68,6 +71,20 @@ struct alignas(64) PairParams {
   ErrCtl err1, err2;
   TileGeom tile;
   const int* order;
+  // fused halo exchange of level n+1 (same protocol and member names as StepParams, so the
+  // face helpers in kernels.cuh work on both): face CTAs acquire `level` before loading,
+  // copy the level-(n+1) face layers of `nxt` (= out1) into the neighbours and the last
+  // one releases level+1.
+  double* nxt;
+  int n_face_ctas;
+  int use_flags;
+  int debug_skip;
+  PeerDev peer[6];
+  const unsigned long long* flags_in;
+  unsigned* shell_counter;
+  unsigned* status;
+  unsigned long long level;
+  unsigned long long timeout_ns;
   // nodes of level 2 that must NOT be produced here: the layer next to a face with a
   // neighbour (their level-1 ghost is not known yet).  skip_lo/hi[d] = 1 when active.
   int skip_lo[3], skip_hi[3];
@@ -77,8 +94,21 @@ struct alignas(64) PairParams {
 // updated by this launch and is not excluded by a skip flag: all per-node predicates
 // fold away and the eight rows of a thread become straight-line code that the compiler
 // can interleave (the dependent FMA chains of one row otherwise expose their latency).
+// one thread: arm the stage's barrier and issue the TMA loads of iteration t (plane z0-2+t)
+template <class Cfg>
+__device__ __forceinline__ void pair_issue(const PairParams& P, uint64_t* full, uint8_t* stage0, int t, int x0,
+                                           int y0, int z0, int nzc) {
+  const int s = t % Cfg::kStages;
+  const int p = z0 - 2 + t;
+  const bool need_b = (t >= 1 && t <= nzc + 2);       // planes z0-1 .. z1
+  uint8_t* st = stage0 + (size_t)s * Cfg::kStageBytes;
+  mbar_arrive_expect_tx(full + s, (uint32_t)(Cfg::kATx + (need_b ? Cfg::kBTx : 0)));
+  tma_load_3d(st, &P.map_a, full + s, P.g.xoff + x0 - 2, y0 - 2, p);
+  if (need_b) tma_load_3d(st + Cfg::kABytes, &P.map_b, full + s, P.g.xoff + x0 - 2, y0 - 1, p);
+}
+
 template <class Cfg, bool FULL, bool XFULL>
-__device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* full, uint64_t* empty, uint8_t* stage0,
+__device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* full, uint8_t* stage0,
                                               double* l1buf, const double* s_sz, int x0, int y0, int z0, int z1,
                                               double& mx1, double& s21, double& mx2, double& s22) {
   constexpr int TX = Cfg::kTX, RPT = Cfg::kRPT, STAGES = Cfg::kStages;
@@ -198,9 +228,8 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
       }
     }
     rzA = ring_c;
-    __syncwarp();
-    if ((tid & 31) == 0) mbar_arrive(empty + s);                 // the stage is free again
-    named_bar_sync(kConsBarrier, Cfg::kConsumers);               // level-1 plane p-1 is complete in smem
+    __syncthreads();          // level-1 plane p-1 is complete in smem AND every thread is done with stage s
+    if (tid == 0 && t + STAGES < iters) pair_issue<Cfg>(P, full, stage0, t + STAGES, x0, y0, z0, nzc);
     // ---- level 2 ----
     const int p2 = p - 2;                                        // level-2 plane completed now
     if (p2 >= z0 && p2 < z1) {
@@ -253,7 +282,6 @@ __global__ void __launch_bounds__(Cfg::kThreads, 1) pair_step_kernel(const __gri
   // LDS/STS with 32-bit addresses instead of generic LD/ST with 64-bit address arithmetic.
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-  uint64_t* empty = full + STAGES;
   double* red = reinterpret_cast<double*>(smem + 128);
   double* s_sz = reinterpret_cast<double*>(smem + 128 + 1024);
   uint8_t* stage0 = smem + Cfg::kBarBytes;
@@ -272,59 +300,41 @@ __global__ void __launch_bounds__(Cfg::kThreads, 1) pair_step_kernel(const __gri
   const int nzc = z1 - z0;
   const int iters = nzc + 4;          // planes z0-2 .. z1+1 of u^n
 
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) {
-      mbar_init(full + s, 1);
-      mbar_init(empty + s, Cfg::kConsumers / 32);
-    }
-    fence_barrier_init();
-  }
-  // z slice of the analytic table for the error epilogue: a global load per plane inside the
-  // loop exposed its full latency to every consumer warp (ncu: top long-scoreboard stall)
-  __syncthreads();
-
   double mx1 = 0.0, s21 = 0.0, mx2 = 0.0, s22 = 0.0;
-  const int warp = threadIdx.x >> 5;
-  if (warp == Cfg::kConsumers / 32) {
-    // ===== producer warp =====
-    const bool leader = (threadIdx.x & 31) == 0;
-    if (leader) {
-      tma_prefetch_desc(&P.map_a);
-      tma_prefetch_desc(&P.map_b);
-    }
-    for (int t = 0; t < iters; ++t) {
-      if (leader) {
-        const int s = t % STAGES;
-        const uint32_t ph = (uint32_t)(t / STAGES) & 1u;
-        mbar_wait(empty + s, ph ^ 1u);
-        const int p = z0 - 2 + t;
-        const bool need_b = (t >= 1 && t <= nzc + 2);       // planes z0-1 .. z1
-        uint8_t* st = stage0 + (size_t)s * Cfg::kStageBytes;
-        mbar_arrive_expect_tx(full + s, (uint32_t)(Cfg::kATx + (need_b ? Cfg::kBTx : 0)));
-        tma_load_3d(st, &P.map_a, full + s, g.xoff + x0 - 2, y0 - 2, p);
-        if (need_b) tma_load_3d(st + Cfg::kABytes, &P.map_b, full + s, g.xoff + x0 - 2, y0 - 1, p);
-      }
-      __syncwarp();
-    }
-  } else {
-    // staged by the consumers only, after the CTA barrier, so the producer's first TMA loads
-    // are already in flight meanwhile
-    for (int i = threadIdx.x; i < iters && i < Cfg::kSzEntries; i += Cfg::kConsumers) {
-      const int k = z0 - 2 + i;
-      s_sz[i] = (k >= 0 && k <= g.n[2] + 1) ? P.sz[k] : 0.0;
-    }
-    named_bar_sync(kConsBarrier, Cfg::kConsumers);
-    // every tile node inside the block, updated by this launch, and not next to a skipped face
+  const int mask = tile_face_mask(P, x0, y0, z0, z1, TX, Cfg::kTY);
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&P.map_a);
+    tma_prefetch_desc(&P.map_b);
+    if (mask) wait_peer_flags(P, mask);      // ghosts of u^n must have arrived before they are loaded
+    for (int t = 0; t < STAGES && t < iters; ++t) pair_issue<Cfg>(P, full, stage0, t, x0, y0, z0, nzc);
+  }
+  // z slice of the analytic table for the error epilogue (a global load per plane inside the
+  // loop exposed its full latency to every warp: ncu, top long-scoreboard stall)
+  for (int i = threadIdx.x; i < iters && i < Cfg::kSzEntries; i += Cfg::kThreads) {
+    const int k = z0 - 2 + i;
+    s_sz[i] = (k >= 0 && k <= g.n[2] + 1) ? P.sz[k] : 0.0;
+  }
+  __syncthreads();
+  {
+    // FULL: tile complete in y and free of skipped rows; XFULL: the same in x
     const bool full_tile = y0 + Cfg::kTY <= T.hi[1] && !(P.skip_lo[1] && y0 <= 1) &&
                            !(P.skip_hi[1] && y0 + Cfg::kTY > g.n[1]);
     const bool xfull = x0 >= T.lo[0] && x0 >= 1 && x0 + TX <= T.hi[0] && !(P.skip_lo[0] && x0 <= 1) &&
                        !(P.skip_hi[0] && x0 + TX > g.n[0]);
     if (full_tile && xfull)
-      pair_consumer<Cfg, true, true>(P, full, empty, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
+      pair_consumer<Cfg, true, true>(P, full, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
     else if (full_tile)
-      pair_consumer<Cfg, true, false>(P, full, empty, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
+      pair_consumer<Cfg, true, false>(P, full, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
     else
-      pair_consumer<Cfg, false, false>(P, full, empty, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
+      pair_consumer<Cfg, false, false>(P, full, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
+    if (mask) {
+      __syncthreads();   // the tile's level n+1 is written (CTA-visible)
+      face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kThreads);
+      __syncthreads();
+      if (threadIdx.x == 0) face_cta_done(P);
+    }
   }
   if (P.err1.out != nullptr) {
     __syncthreads();

@@ -61,7 +61,7 @@ const Variant kVariants[] = {
 constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
 // ---- temporal-blocking (two steps per pass) variants ----
-using PCfg0 = PairCfg<64, 8, 4, 4>;    // 64 x 32 tile, 288 threads, 4-stage ring (~188 KB)
+using PCfg0 = PairCfg<64, 8, 4, 4>;    // 64 x 32 tile, 256 threads, 4-stage ring (~194 KB)
 using PCfg1 = PairCfg<64, 8, 4, 3>;    // 3-stage ring (~150 KB)
 using PCfg2 = PairCfg<128, 8, 4, 2>;   // 128 x 32 tile, 544 threads, 2-stage ring (~215 KB)
 using PCfg3 = PairCfg<64, 4, 8, 4>;    // 64 x 32 tile, 4 rows per thread: 544 threads (16 consumer warps)
@@ -124,10 +124,12 @@ struct W3dPlan {
   const double* ct_table;          // optional device table of cos(a_t t_n), host-fed
   // temporal blocking: four arrays (0,1 = desc.field, 2,3 = aux), two TMA maps each
   double* arr[4];
+  double* peer_arr[6][4];          // the neighbours' four arrays, per face
   CUtensorMap pmap_a[4], pmap_b[4];
   int pair_variant;
   TileGeom ptile;
-  int pn_ctas;
+  int pn_ctas, pn_face_ctas;
+  BoxTable shell;                  // layer next to faces with a neighbour (fix-up pass)
   bool pair_ready;
   long long launches;
   char text[768];
@@ -300,6 +302,20 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
     const int lo[3] = {1, 1, 1}, hi[3] = {b.n[0] + 1, b.n[1] + 1, b.n[2] + 1};
     plan_tiles(p, lo, hi, desc->zchunk, &p->tile);
   }
+  // shell = the layer next to every face with a neighbour, as disjoint boxes (z slabs, then y, then x)
+  std::memset(&p->shell, 0, sizeof(p->shell));
+  {
+    int lo[3] = {1, 1, 1}, hi[3] = {b.n[0] + 1, b.n[1] + 1, b.n[2] + 1};
+    for (int d = 2; d >= 0; --d) {
+      const int ilo = 1 + (desc->peer[d * 2].active ? 1 : 0);
+      const int ihi = std::max(ilo, b.n[d] + 1 - (desc->peer[d * 2 + 1].active ? 1 : 0));
+      int l2[3] = {lo[0], lo[1], lo[2]}, h2[3] = {hi[0], hi[1], hi[2]};
+      if (ilo > lo[d]) { h2[d] = ilo; add_box(&p->shell, l2, h2); h2[d] = hi[d]; }
+      if (ihi < hi[d]) { l2[d] = ihi; add_box(&p->shell, l2, h2); }
+      lo[d] = ilo;
+      hi[d] = ihi;
+    }
+  }
   p->n_ctas = p->tile.ntx * p->tile.nty * p->tile.nchunks;
   if (p->n_ctas > W3D_MAX_PARTIALS) {
     const int need = p->n_ctas;
@@ -393,7 +409,7 @@ int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double 
     for (int q = 0; q < P.err.n_bcast; ++q) P.err.bcast[q] = p->d.err_table_peer[q] + off;
   }
   P.tile = p->tile;
-  P.order = p->order_dev + ((s & 1) ? W3D_MAX_PARTIALS : 0);
+  P.order = p->n_face_ctas > 0 ? p->order_dev : nullptr;   // identity when nothing to reorder
   P.n_face_ctas = p->n_face_ctas;
   P.use_flags = p->any_peer ? 1 : 0;
   const int nxt = (s & 1) ^ 1;
@@ -464,13 +480,14 @@ int w3d_step_box(W3dPlan* p, int s, double a, double b, double cscale, double ct
   return W3D_OK;
 }
 
-int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, int pair_variant, int zchunk) {
+int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const* peer_aux, int pair_variant,
+                          int zchunk) {
   if (!p || !aux0 || !aux1) return fail(W3D_EINVAL, "null argument");
   if ((reinterpret_cast<uintptr_t>(aux0) | reinterpret_cast<uintptr_t>(aux1)) & 15)
     return fail(W3D_EINVAL, "aux arrays must be 16-byte aligned");
   EncodeTiledFn enc = get_encode();
   if (!enc) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled is not available from the driver");
-  p->pair_variant = pair_variant >= 0 && pair_variant < kNumPairVariants ? pair_variant : 0;
+  p->pair_variant = pair_variant >= 0 && pair_variant < kNumPairVariants ? pair_variant : 4;   // best of the measured sweep
   const PairVariant& v = kPairVariants[p->pair_variant];
   p->arr[0] = p->d.field[0]; p->arr[1] = p->d.field[1]; p->arr[2] = aux0; p->arr[3] = aux1;
   const cuuint64_t dims[3] = {(cuuint64_t)p->g.pitch, (cuuint64_t)(p->g.n[1] + 2), (cuuint64_t)(p->g.n[2] + 2)};
@@ -516,6 +533,33 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, int pair_varia
   t.nchunks = (ez + t.zc - 1) / t.zc;
   p->pn_ctas = t.ntx * t.nty * t.nchunks;
   if (p->pn_ctas > W3D_MAX_PARTIALS) return fail(W3D_EINVAL, "pair kernel needs %d CTAs, limit %d", p->pn_ctas, W3D_MAX_PARTIALS);
+  // neighbours' arrays by index; face CTAs first in the block -> tile table of the pair kernel
+  for (int f = 0; f < 6; ++f) {
+    p->peer_arr[f][0] = p->d.peer[f].field[0];
+    p->peer_arr[f][1] = p->d.peer[f].field[1];
+    p->peer_arr[f][2] = peer_aux ? peer_aux[f * 2] : nullptr;
+    p->peer_arr[f][3] = peer_aux ? peer_aux[f * 2 + 1] : nullptr;
+    if (p->d.peer[f].active && (!p->peer_arr[f][2] || !p->peer_arr[f][3]))
+      return fail(W3D_EINVAL, "face %d has a neighbour but no peer aux arrays were given", f);
+  }
+  {
+    std::vector<int> face, rest;
+    for (int w = 0; w < p->pn_ctas; ++w) {
+      const int tx = w % t.ntx, ty = (w / t.ntx) % t.nty, ch = w / (t.ntx * t.nty);
+      const int lo[3] = {t.x0 + tx * v.tx, t.lo[1] + ty * v.ty, t.lo[2] + ch * t.zc};
+      const int hi[3] = {lo[0] + v.tx, lo[1] + v.ty, std::min(lo[2] + t.zc, t.hi[2])};
+      bool is_face = false;
+      for (int d = 0; d < 3; ++d) {
+        if (p->d.peer[d * 2].active && lo[d] <= 1 && hi[d] > 1) is_face = true;
+        if (p->d.peer[d * 2 + 1].active && lo[d] <= p->g.n[d] && hi[d] > p->g.n[d]) is_face = true;
+      }
+      (is_face ? face : rest).push_back(w);
+    }
+    p->pn_face_ctas = (int)face.size();
+    face.insert(face.end(), rest.begin(), rest.end());
+    CUDA_TRY(cudaMemcpy(p->order_dev + W3D_MAX_PARTIALS, face.data(), face.size() * sizeof(int),
+                        cudaMemcpyHostToDevice));
+  }
   p->pair_ready = true;
   const size_t used = std::strlen(p->text);
   snprintf(p->text + used, sizeof(p->text) - used, " || %s (%d thr, %d B smem): tiles %dx%d zc %d chunks %d -> %d CTAs",
@@ -523,7 +567,17 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, int pair_varia
   return W3D_OK;
 }
 
-int w3d_step_pair(W3dPlan* p, int cur, int prev, int out1, int out2, double a1, double b1, double cscale1,
+namespace {
+void set_bcast(const W3dPlan* p, ErrCtl* e, double* err_out) {
+  if (err_out && p->d.err_table && p->d.n_err_peers > 0) {
+    const ptrdiff_t off = err_out - p->d.err_table;   // same offset in every rank's table
+    e->n_bcast = std::min(p->d.n_err_peers, 7);
+    for (int q = 0; q < e->n_bcast; ++q) e->bcast[q] = p->d.err_table_peer[q] + off;
+  }
+}
+}  // namespace
+
+int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, double a1, double b1, double cscale1,
                   double ct1, double a2, double b2, double cscale2, double ct2, double* err1, double* err2,
                   void* stream) {
   if (!p || !p->pair_ready) return fail(W3D_EINVAL, "w3d_plan_enable_pairs has not been called");
@@ -547,13 +601,74 @@ int w3d_step_pair(W3dPlan* p, int cur, int prev, int out1, int out2, double a1, 
   P.ct1 = ct1; P.ct2 = ct2;
   P.err1 = err_ctl(p, 0, err1);
   P.err2 = err_ctl(p, 1, err2);
+  set_bcast(p, &P.err1, err1);
+  set_bcast(p, &P.err2, err2);
   P.tile = p->ptile;
-  P.order = nullptr;
+  P.order = p->pn_face_ctas > 0 ? p->order_dev + W3D_MAX_PARTIALS : nullptr;   // identity when nothing to reorder
   for (int d = 0; d < 3; ++d) {
     P.skip_lo[d] = p->d.peer[d * 2].active ? 1 : 0;
     P.skip_hi[d] = p->d.peer[d * 2 + 1].active ? 1 : 0;
   }
+  // fused exchange of level s+1 (the array out1)
+  P.nxt = p->arr[out1];
+  P.n_face_ctas = p->pn_face_ctas;
+  P.use_flags = p->any_peer ? 1 : 0;
+  for (int f = 0; f < 6; ++f) {
+    const W3dPeer& q = p->d.peer[f];
+    P.peer[f].active = q.active;
+    P.peer[f].ghost_index = q.ghost_index;
+    P.peer[f].field = p->peer_arr[f][out1];
+    P.peer[f].pitch = q.pitch;
+    P.peer[f].plane = q.plane;
+    P.peer[f].flag = q.flag;
+  }
+  P.flags_in = p->d.flags_in;
+  P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
+  P.status = p->d.status;
+  P.level = (unsigned long long)s;
+  P.timeout_ns = (unsigned long long)(p->d.spin_timeout_ms > 0 ? p->d.spin_timeout_ms : 10000) * 1000000ull;
   v.kernel<<<p->pn_ctas, v.threads, v.smem, static_cast<cudaStream_t>(stream)>>>(P);
+  CUDA_TRY(cudaGetLastError());
+  ++p->launches;
+  return W3D_OK;
+}
+
+int w3d_step_fixup(W3dPlan* p, int level, int cur, int prev, int out, double a, double b, double cscale,
+                   double ct, double* err_out, void* stream) {
+  if (!p || !p->pair_ready) return fail(W3D_EINVAL, "w3d_plan_enable_pairs has not been called");
+  if (cur < 0 || cur > 3 || prev < 0 || prev > 3 || out < 0 || out > 3 || cur == out || prev == out)
+    return fail(W3D_EINVAL, "bad array indices");
+  const long long nodes = p->shell.prefix[p->shell.nboxes];
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (nodes == 0) {
+    if (err_out) CUDA_TRY(cudaMemsetAsync(err_out, 0, 2 * sizeof(double), st));
+    return W3D_OK;
+  }
+  StepParams P;
+  fill_common(p, &P, level, a, b, cscale, ct);
+  P.ct_ptr = nullptr;
+  P.cur = p->arr[cur];
+  P.nxt = p->arr[out];
+  P.prev_sep = p->arr[prev];
+  P.err = err_ctl(p, 2, err_out);
+  set_bcast(p, &P.err, err_out);
+  P.boxes = p->shell;
+  P.use_flags = p->any_peer ? 1 : 0;
+  for (int f = 0; f < 6; ++f) {
+    const W3dPeer& q = p->d.peer[f];
+    P.peer[f].active = q.active;
+    P.peer[f].ghost_index = q.ghost_index;
+    P.peer[f].field = p->peer_arr[f][out];
+    P.peer[f].pitch = q.pitch;
+    P.peer[f].plane = q.plane;
+    P.peer[f].flag = q.flag;
+  }
+  P.flags_in = p->d.flags_in;
+  P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
+  P.level = (unsigned long long)level;     // waits for `level`, releases level + 1
+  const int blocks = (int)std::max<long long>(1, std::min<long long>((nodes + 1023) / 1024, (long long)p->num_sms * 4));
+  P.n_face_ctas = blocks;
+  fixup_kernel<<<blocks, 256, 0, st>>>(P);
   CUDA_TRY(cudaGetLastError());
   ++p->launches;
   return W3D_OK;

@@ -128,11 +128,22 @@ int w3d_step_box(W3dPlan* plan, int s, double a, double b, double cscale, double
  * writes level n+1 to `out1` and level n+2 to `out2` (all four distinct).  (a,b,cscale,ct)
  * are given per produced level.  Nodes next to a face that has a neighbour are left out of
  * `out2` (their level-n+1 ghost is not known inside the pass); the caller finishes them
- * with w3d_step_box after the exchange of level n+1. */
-int w3d_plan_enable_pairs(W3dPlan* plan, double* aux0, double* aux1, int pair_variant, int zchunk);
-int w3d_step_pair(W3dPlan* plan, int cur, int prev, int out1, int out2, double a1, double b1, double cscale1,
-                  double ct1, double a2, double b2, double cscale2, double ct2, double* err1, double* err2,
-                  void* stream);
+ * with w3d_step_fixup after the exchange of level n+1.  peer_aux: for every face f with a
+ * neighbour, peer_aux[2f] and peer_aux[2f+1] are that neighbour's aux0/aux1 mapped here. */
+int w3d_plan_enable_pairs(W3dPlan* plan, double* aux0, double* aux1, double* const* peer_aux /* [12] or NULL */,
+                          int pair_variant, int zchunk);
+/* s = level held by `cur`.  Face CTAs acquire the neighbours' flags for level s, and after
+ * their tile is written they copy the level-(s+1) face layers of `out1` into the neighbours'
+ * ghost layers; the last one releases level s+1. */
+int w3d_step_pair(W3dPlan* plan, int s, int cur, int prev, int out1, int out2, double a1, double b1,
+                  double cscale1, double ct1, double a2, double b2, double cscale2, double ct2, double* err1,
+                  double* err2, void* stream);
+/* Fix-up pass: out = a*cur + b*prev + cscale*Laplace(cur) on the layer next to every face with a
+ * neighbour (the nodes w3d_step_pair left out), after acquiring the flags for `level` (= the
+ * level held by `cur`, whose ghosts the neighbours deliver during their pair pass); stores go to
+ * the local array and into the neighbours' ghost layers; releases level + 1. */
+int w3d_step_fixup(W3dPlan* plan, int level, int cur, int prev, int out, double a, double b, double cscale,
+                   double ct, double* err_out, void* stream);
 
 /* NCCL-baseline helpers (K5): contiguous face buffers of the unknowns of the two
  * other axes, fastest index first.  ghost=0 packs/unpacks the edge layer of

@@ -66,8 +66,9 @@ def lib() -> C.CDLL:
     l.w3d_step_fused.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
     l.w3d_step_tma.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, i32p, i32p, vp, C.c_int, vp]
     l.w3d_step_box.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, i32p, i32p, vp, C.c_int, vp]
-    l.w3d_plan_enable_pairs.argtypes = [vp, vp, vp, C.c_int, C.c_int]
-    l.w3d_step_pair.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, dbl, dbl, dbl, dbl, dbl, dbl, dbl, dbl, vp, vp, vp]
+    l.w3d_plan_enable_pairs.argtypes = [vp, vp, vp, C.POINTER(vp), C.c_int, C.c_int]
+    l.w3d_step_pair.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, dbl, dbl, dbl, dbl, dbl, dbl, dbl, dbl, vp, vp, vp]
+    l.w3d_step_fixup.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
     l.w3d_pack_face.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
     l.w3d_unpack_face.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
     l.w3d_wrap_axis.argtypes = [vp, C.c_int, C.c_int, vp]
@@ -207,17 +208,27 @@ class CudaPlan:
         check(lib().w3d_step_box(self._h, s, a, b, cscale, ct, _box(lo), _box(hi), self._err_ptr(err_out),
                                  slot, stream_ptr()))
 
-    def enable_pairs(self, aux0: torch.Tensor, aux1: torch.Tensor, pair_variant: int = -1, zchunk: int = 0) -> None:
-        """Register two more arrays (same layout) so that two steps can be fused per pass."""
+    def enable_pairs(self, aux0: torch.Tensor, aux1: torch.Tensor, pair_variant: int = -1, zchunk: int = 0,
+                     peer_aux: Optional[dict] = None) -> None:
+        """Register two more arrays (same layout) so that two steps can be fused per pass.
+
+        peer_aux: face index -> (aux0 address, aux1 address) of that neighbour's arrays."""
         for a in (aux0, aux1):
             assert a.is_cuda and a.dtype == torch.float64 and a.shape == self.fields[0].shape and a.is_contiguous()
         self.aux = [aux0, aux1]
-        check(lib().w3d_plan_enable_pairs(self._h, aux0.data_ptr(), aux1.data_ptr(), pair_variant, zchunk))
+        table = (C.c_void_p * 12)()
+        for f, (p0, p1) in (peer_aux or {}).items():
+            table[2 * f], table[2 * f + 1] = p0, p1
+        check(lib().w3d_plan_enable_pairs(self._h, aux0.data_ptr(), aux1.data_ptr(), table, pair_variant, zchunk))
 
-    def step_pair(self, cur: int, prev: int, out1: int, out2: int, lvl1, lvl2, err1=None, err2=None) -> None:
-        """lvl1 / lvl2 = (a, b, cscale, ct) of the two produced levels; arrays by index 0..3."""
-        check(lib().w3d_step_pair(self._h, cur, prev, out1, out2, *lvl1, *lvl2, self._err_ptr(err1),
+    def step_pair(self, s: int, cur: int, prev: int, out1: int, out2: int, lvl1, lvl2, err1=None, err2=None) -> None:
+        """s = level held by array `cur`; lvl1 / lvl2 = (a, b, cscale, ct) of the two produced levels."""
+        check(lib().w3d_step_pair(self._h, s, cur, prev, out1, out2, *lvl1, *lvl2, self._err_ptr(err1),
                                   self._err_ptr(err2), stream_ptr()))
+
+    def step_fixup(self, level: int, cur: int, prev: int, out: int, lvl, err=None) -> None:
+        """Finish level+1 on the layer next to faces with a neighbour (see w3d_step_fixup)."""
+        check(lib().w3d_step_fixup(self._h, level, cur, prev, out, *lvl, self._err_ptr(err), stream_ptr()))
 
     def pack_face(self, parity: int, axis: int, side: int, buf: torch.Tensor, ghost: bool = False) -> None:
         check(lib().w3d_pack_face(self._h, parity, axis, side, int(ghost), buf.data_ptr(), stream_ptr()))

@@ -34,6 +34,7 @@ from .decomp import RankBlock, local_tables, plan_all, plan_rank
 from .exchange import step_coeffs
 
 _FLAG_BYTES = 256     # 6 flag words + padding, at the head of the symmetric buffer
+_SLOTS = 2            # error-table entries per rank and level (step kernel, fix-up pass)
 
 
 def _field_bytes(n: Sequence[int]) -> int:
@@ -45,6 +46,7 @@ class FusedSolver:
     def __init__(self, p: WaveProblem, dims: Sequence[int] = (1, 1, 1), device: Optional[torch.device] = None,
                  group=None, every: int = 2, variant: int = -1, zchunk: int = 0, use_graph: bool = True,
                  spin_timeout_ms: int = 0, pair: bool = False, pair_variant: int = -1):
+        self._launches_per_run = p.K
         self.p, self.dims, self.every = p, tuple(int(d) for d in dims), every
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -60,9 +62,11 @@ class FusedSolver:
         fbytes = (fbytes + 255) // 256 * 256
         # error table: one row per rank, (K+1) x (max, sum sq); every rank holds a full copy
         # that the other ranks' kernels fill over NVLink
-        tbytes = (self.world * (p.K + 1) * 16 + 255) // 256 * 256
+        tbytes = (self.world * (p.K + 1) * _SLOTS * 16 + 255) // 256 * 256
         f0 = _FLAG_BYTES + tbytes                     # offset of the first field array
-        total = f0 + 2 * fbytes
+        self.pair = bool(pair)
+        narr = 4 if self.pair else 2                  # temporal blocking needs two more arrays
+        total = f0 + narr * fbytes
         # ---- storage: symmetric when there are real peers ----
         self.symm = None
         if self.world > 1:
@@ -80,14 +84,19 @@ class FusedSolver:
         self.flags = buf[:_FLAG_BYTES].view(torch.int64)
         self.f = [buf[f0 + q * fbytes: f0 + q * fbytes + nel * 8].view(torch.float64).view(shape)
                   for q in range(2)]
-        self.table = buf[_FLAG_BYTES: _FLAG_BYTES + self.world * (p.K + 1) * 16].view(torch.float64).view(
-            self.world, p.K + 1, 2)
+        self.aux = [buf[f0 + q * fbytes: f0 + q * fbytes + nel * 8].view(torch.float64).view(shape)
+                    for q in range(2, narr)]
+        # (world, K+1, slots, 2): slot 0/1 = the step kernels, slot 1 also = the fix-up pass of a pair
+        self.table = buf[_FLAG_BYTES: _FLAG_BYTES + self.world * (p.K + 1) * _SLOTS * 16].view(torch.float64).view(
+            self.world, p.K + 1, _SLOTS, 2)
         self.tab = [torch.from_numpy(t).to(self.device) for t in local_tables(p, blk)]
         self.status = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.ws = torch.zeros(cuda.workspace_bytes(), dtype=torch.uint8, device=self.device)
-        self.trace = self.table[self.rank]            # my row: the kernel writes it here and in every peer's copy
+        self.trace = self.table[self.rank, :, 0]      # my row: the kernel writes it here and in every peer's copy
+        self.trace_fix = self.table[self.rank, :, 1]  # fix-up pass of the two-step scheme
         # ---- peers ----
         peers: Dict[int, cuda.PeerSpec] = {}
+        peer_aux: Dict[int, Tuple[int, int]] = {}
         for d in range(3):
             for s in range(2):
                 r = blk.nbr[d][s]
@@ -102,6 +111,7 @@ class FusedSolver:
                     field_ptrs=(base + f0, base + f0 + fbytes), ghost_index=ghost,
                     pitch=pshape[2], plane=pshape[1] * pshape[2],
                     flag_ptr=base + 8 * (d * 2 + (1 - s)))
+                peer_aux[d * 2 + s] = (base + f0 + 2 * fbytes, base + f0 + 3 * fbytes)
         self.plan = cuda.CudaPlan(blk.n, self.f, self.tab, p.coeffs(), self.flags, self.status, self.ws,
                                   peers=peers, variant=variant, zchunk=zchunk, spin_timeout_ms=spin_timeout_ms,
                                   err_table_ptr=base_ptrs[self.rank if self.world > 1 else 0] + _FLAG_BYTES,
@@ -110,14 +120,10 @@ class FusedSolver:
         self.ct = time_table(p)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.kernel_launches = 0
-        # ---- temporal blocking (two steps per pass): two more arrays ----
-        self.pair = bool(pair)
+        # ---- temporal blocking (two steps per pass) ----
         self.final_index = None          # array index (0..3) holding level K after run_steps in pair mode
         if self.pair:
-            if self.world > 1 or any(p.periodic):
-                raise NotImplementedError("pair mode currently supports one GPU with Dirichlet boundaries")
-            self.aux = [torch.zeros(shape, dtype=torch.float64, device=self.device) for _ in range(2)]
-            self.plan.enable_pairs(self.aux[0], self.aux[1], pair_variant, zchunk)
+            self.plan.enable_pairs(self.aux[0], self.aux[1], pair_variant, zchunk, peer_aux)
 
     # ------------------------------------------------------------------
     def describe(self) -> str:
@@ -134,7 +140,7 @@ class FusedSolver:
         All ranks must have finished this before any rank's first step may push
         into their ghosts, hence the barrier."""
         self.plan.init()
-        self.trace.zero_()                               # only my own row: peers clear theirs
+        self.table[self.rank].zero_()                    # only my own row: peers clear theirs
         self.barrier()
 
     def step(self, n: int, want_err: bool = True) -> None:
@@ -151,23 +157,30 @@ class FusedSolver:
             self.step(n, n % self.every == 0)
 
     def _enqueue_pairs(self, last: int) -> None:
-        """Levels 1..last with two steps per launch (plus one single step if `last` is odd).
+        """Levels 1..last with two steps per pass (plus one single step if `last` is odd).
 
         Array roles rotate over the four arrays: (cur, prev) -> (out1, out2) = (0,1)->(2,3),
-        (3,2)->(0,1), (1,0)->(2,3), ..."""
+        (3,2)->(0,1), (1,0)->(2,3), ...  With neighbours (or periodic axes) every pair is two
+        launches: the pair pass (which also ships the level-(n+1) faces) and the fix-up pass
+        that finishes level n+2 next to those faces and ships them."""
         n = 0
         cur, prev = 0, 1
         if last % 2 == 1:                 # odd count: the Taylor step goes alone, in place
             self.step(1, 1 % self.every == 0)
             n, cur, prev = 1, 1, 0
+        has_faces = any(r >= 0 for ax in self.blk.nbr for r in ax)
         while n < last:
             out1, out2 = (2, 3) if cur in (0, 1) else (0, 1)
             l1 = step_coeffs(n + 1) + (float(self.ct[n + 1]),)
             l2 = step_coeffs(n + 2) + (float(self.ct[n + 2]),)
-            e1 = self.trace[n + 1] if (n + 1) % self.every == 0 else None
-            e2 = self.trace[n + 2] if (n + 2) % self.every == 0 else None
-            self.plan.step_pair(cur, prev, out1, out2, l1, l2, e1, e2)
+            w1 = (n + 1) % self.every == 0
+            w2 = (n + 2) % self.every == 0
+            self.plan.step_pair(n, cur, prev, out1, out2, l1, l2, self.trace[n + 1] if w1 else None,
+                                self.trace[n + 2] if w2 else None)
             self.kernel_launches += 1
+            if has_faces:
+                self.plan.step_fixup(n + 1, out1, cur, out2, l2, self.trace_fix[n + 2] if w2 else None)
+                self.kernel_launches += 1
             n += 2
             cur, prev = out2, out1
         self.final_index = cur
@@ -182,8 +195,11 @@ class FusedSolver:
         self.barrier()
         g = torch.cuda.CUDAGraph()
         self.init()
+        l0 = self.kernel_launches
         with torch.cuda.graph(g):
             self._enqueue_steps(1, self.p.K)
+        self._launches_per_run = self.kernel_launches - l0
+        self.kernel_launches = l0
         self.graph = g
         self.barrier()
 
@@ -191,7 +207,7 @@ class FusedSolver:
         """Enqueue all K steps on the current stream (graph replay if captured)."""
         if self.use_graph and self.graph is not None:
             self.graph.replay()
-            self.kernel_launches += (self.p.K + 1) // 2 if self.pair else self.p.K
+            self.kernel_launches += self._launches_per_run
         else:
             self._enqueue_steps(1, self.p.K)
 
@@ -207,11 +223,12 @@ class FusedSolver:
         Every rank's kernel has already stored its row into every other rank's table
         (P2P stores from the error epilogue), so this is a purely local read — call it
         after :meth:`barrier`.  The sum is taken in fixed rank order."""
-        tc = self.table.cpu()                            # (world, K+1, 2)
-        mx = tc[:, :, 0].max(dim=0).values
-        s2 = tc[0, :, 1].clone()
-        for r in range(1, self.world):
-            s2 += tc[r, :, 1]
+        tc = self.table.cpu()                            # (world, K+1, slots, 2)
+        mx = tc[..., 0].amax(dim=(0, 2))
+        s2 = torch.zeros(tc.shape[1], dtype=torch.float64)
+        for r in range(self.world):                      # fixed rank / slot order
+            for q in range(tc.shape[2]):
+                s2 += tc[r, :, q, 1]
         p = self.p
         return [(n, n * p.tau, float(mx[n]), math.sqrt(float(s2[n]) / p.n_unknowns))
                 for n in range(1, p.K + 1) if n % self.every == 0]
@@ -225,7 +242,7 @@ class FusedSolver:
         self.barrier()
         ev[0].record()
         self.plan.init()
-        self.trace.zero_()
+        self.table[self.rank].zero_()
         self.barrier()          # flags must be reset everywhere before anyone pushes
         ev[1].record()
         self.run_steps()

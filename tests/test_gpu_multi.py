@@ -36,8 +36,8 @@ def _work(rank, world, mode, dims, bc, N, K, graph):
     from mpi_cuda_b200.parallel.fused import FusedSolver
     dev = torch.device("cuda", rank)
     p = WaveProblem(N, 2.0, 1e-3, K, bc=bc)
-    if mode == "fused":
-        s = FusedSolver(p, dims, dev, every=2, use_graph=graph, spin_timeout_ms=5000)
+    if mode in ("fused", "pair"):
+        s = FusedSolver(p, dims, dev, every=2, use_graph=graph, spin_timeout_ms=5000, pair=(mode == "pair"))
         r = s.run()
         r2 = s.run()
         assert r.trace == r2.trace
@@ -50,7 +50,7 @@ def _ngpu():
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("mode", ["nccl", "fused"])
+@pytest.mark.parametrize("mode", ["nccl", "fused", "pair"])
 @pytest.mark.parametrize("dims,bc", [((1, 1, 2), "ddd"), ((1, 2, 1), "ddp"), ((2, 1, 1), "ddd"), ((1, 1, 2), "ddp")])
 def test_two_gpu_trace_equals_one_gpu(mode, dims, bc):
     N, K = (72, 60, 52), 8
@@ -72,10 +72,11 @@ def test_two_gpu_skewed_ranks_still_agree():
             assert a[2] == b[2] and abs(a[3] - b[3]) <= 1e-12 * b[3]
 
 
-def test_two_gpu_fused_graph():
+@pytest.mark.parametrize("mode", ["fused", "pair"])
+def test_two_gpu_fused_graph(mode):
     N, K = (96, 64, 64), 10
     base, _ = cpu.solve(WaveProblem(N, 2.0, 1e-3, K), every=2)
-    out = spawn(_work, 2, ("fused", (1, 1, 2), "ddd", N, K, True), backend="nccl")
+    out = spawn(_work, 2, (mode, (1, 1, 2), "ddd", N, K, True), backend="nccl")
     for a, b in zip(out[0], base):
         assert a[2] == b[2]
 
@@ -86,7 +87,7 @@ def test_four_gpu_blocks(dims):
         pytest.skip("needs 4 GPUs")
     N, K = (80, 72, 64), 8
     base, _ = cpu.solve(WaveProblem(N, 2.0, 1e-3, K, bc="dpd"), every=2)
-    out = spawn(_work, 4, ("fused", dims, "dpd", N, K, False), backend="nccl")
+    out = spawn(_work, 4, ("pair" if dims[2] == 4 else "fused", dims, "dpd", N, K, False), backend="nccl")
     for a, b in zip(out[0], base):
         assert a[2] == b[2]
 
