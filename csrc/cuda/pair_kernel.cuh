@@ -68,6 +68,7 @@ struct alignas(64) PairParams {
   const double* sz;
   double a1, b1, c1x, c1y, c1z, ct1;   // level n+1 coefficients / time factor
   double a2, b2, c2x, c2y, c2z, ct2;   // level n+2
+  const double* ct_ptr;                // if non-null: ct1 = ct_ptr[0], ct2 = ct_ptr[1] (host-fed device table)
   ErrCtl err1, err2;
   TileGeom tile;
   const int* order;
@@ -124,6 +125,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
   const bool x_in = gx >= 1 && gx <= g.n[0];                 // inside the local block
   const bool x_ok = gx >= T.lo[0] && gx < T.hi[0];           // this launch updates it
   const bool want1 = P.err1.out != nullptr, want2 = P.err2.out != nullptr;
+  const double ct1 = P.ct_ptr ? __ldg(P.ct_ptr) : P.ct1, ct2 = P.ct_ptr ? __ldg(P.ct_ptr + 1) : P.ct2;
   double acc1[RPT], zA[RPT], acc2[RPT], zL[RPT], sxy[RPT];
   bool in1[RPT], st1[RPT], st2[RPT];
   const double sxv = x_in ? P.sx[gx] : 0.0;
@@ -195,7 +197,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
       for (int r = 0; r < RPT; ++r)
         if (st1[r]) o[r * pitch] = l1c[r];
       if (want1) {
-        const double szt = s_sz[t - 1] * P.ct1;      // s_sz[i] = sz[z0 - 2 + i]
+        const double szt = s_sz[t - 1] * ct1;      // s_sz[i] = sz[z0 - 2 + i]
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
           if (st1[r]) {
@@ -243,7 +245,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
         for (int r = 0; r < RPT; ++r)
           if (st2[r]) o[r * pitch] = v2[r];
         if (want2) {
-          const double szt = s_sz[t - 2] * P.ct2;
+          const double szt = s_sz[t - 2] * ct2;
 #pragma unroll
           for (int r = 0; r < RPT; ++r) {
             if (st2[r]) {

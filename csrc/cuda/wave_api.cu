@@ -599,6 +599,7 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
   P.a1 = a1; P.b1 = b1; P.c1x = cscale1 * p->d.coef[0]; P.c1y = cscale1 * p->d.coef[1]; P.c1z = cscale1 * p->d.coef[2];
   P.a2 = a2; P.b2 = b2; P.c2x = cscale2 * p->d.coef[0]; P.c2y = cscale2 * p->d.coef[1]; P.c2z = cscale2 * p->d.coef[2];
   P.ct1 = ct1; P.ct2 = ct2;
+  P.ct_ptr = p->ct_table ? p->ct_table + (s + 1) : nullptr;
   P.err1 = err_ctl(p, 0, err1);
   P.err2 = err_ctl(p, 1, err2);
   set_bcast(p, &P.err1, err1);
@@ -645,8 +646,7 @@ int w3d_step_fixup(W3dPlan* p, int level, int cur, int prev, int out, double a, 
     return W3D_OK;
   }
   StepParams P;
-  fill_common(p, &P, level, a, b, cscale, ct);
-  P.ct_ptr = nullptr;
+  fill_common(p, &P, level, a, b, cscale, ct);   // (sets ct_ptr = ct_table + level + 1 when a table is attached)
   P.cur = p->arr[cur];
   P.nxt = p->arr[out];
   P.prev_sep = p->arr[prev];

@@ -38,11 +38,13 @@ def resolve_dims(p: WaveProblem, decomp: str, world: int):
 
 def solve(p: WaveProblem, backend: str = "auto", decomp: str = "block", threads: int = 1, every: int = 2,
           ranks: int = 1, verbose: bool = False, check_cfl: bool = True, variant: int = -1,
-          zchunk: int = 0, use_graph: bool = True, device: Optional[torch.device] = None) -> RunResult:
+          zchunk: int = 0, use_graph: bool = True, device: Optional[torch.device] = None,
+          pair: bool = True) -> RunResult:
     """Run the whole simulation and return trace + timings.
 
     ``ranks`` is only used by ``cpu-ranks`` (in-process ranks); for ``gloo`` /
     ``nccl`` / ``fused`` the rank count is the torch.distributed world size.
+    ``pair`` (fused backend): temporal blocking, two time steps per pass over memory.
     """
     p.check_cfl(strict=check_cfl)
     if backend == "auto":
@@ -84,7 +86,7 @@ def solve(p: WaveProblem, backend: str = "auto", decomp: str = "block", threads:
         from ..parallel.fused import FusedSolver
         dev = device or torch.device("cuda", torch.cuda.current_device())
         dims = resolve_dims(p, decomp, _world())
-        s = FusedSolver(p, dims, dev, every=every, variant=variant, zchunk=zchunk, use_graph=use_graph)
+        s = FusedSolver(p, dims, dev, every=every, variant=variant, zchunk=zchunk, use_graph=use_graph, pair=pair)
         res = s.run()
     rank = dist.get_rank() if dist.is_initialized() else 0
     if verbose and rank == 0:

@@ -163,27 +163,37 @@ class FusedSolver:
         (3,2)->(0,1), (1,0)->(2,3), ...  With neighbours (or periodic axes) every pair is two
         launches: the pair pass (which also ships the level-(n+1) faces) and the fix-up pass
         that finishes level n+2 next to those faces and ships them."""
+        n = self.pair_begin(last)
+        while n < last:
+            n = self.pair_advance(n)
+
+    def pair_begin(self, last: int) -> int:
+        """Start a pair-mode run of `last` steps; returns the level reached (0, or 1 if odd)."""
+        self._cur, self._prev = 0, 1
         n = 0
-        cur, prev = 0, 1
         if last % 2 == 1:                 # odd count: the Taylor step goes alone, in place
             self.step(1, 1 % self.every == 0)
-            n, cur, prev = 1, 1, 0
-        has_faces = any(r >= 0 for ax in self.blk.nbr for r in ax)
-        while n < last:
-            out1, out2 = (2, 3) if cur in (0, 1) else (0, 1)
-            l1 = step_coeffs(n + 1) + (float(self.ct[n + 1]),)
-            l2 = step_coeffs(n + 2) + (float(self.ct[n + 2]),)
-            w1 = (n + 1) % self.every == 0
-            w2 = (n + 2) % self.every == 0
-            self.plan.step_pair(n, cur, prev, out1, out2, l1, l2, self.trace[n + 1] if w1 else None,
-                                self.trace[n + 2] if w2 else None)
+            n, self._cur, self._prev = 1, 1, 0
+        self.final_index = self._cur
+        return n
+
+    def pair_advance(self, n: int, force_err: bool = False) -> int:
+        """Levels n+1 and n+2 from level n; returns n + 2."""
+        cur, prev = self._cur, self._prev
+        out1, out2 = (2, 3) if cur in (0, 1) else (0, 1)
+        l1 = step_coeffs(n + 1) + (float(self.ct[n + 1]),)
+        l2 = step_coeffs(n + 2) + (float(self.ct[n + 2]),)
+        w1 = force_err or (n + 1) % self.every == 0
+        w2 = force_err or (n + 2) % self.every == 0
+        self.plan.step_pair(n, cur, prev, out1, out2, l1, l2, self.trace[n + 1] if w1 else None,
+                            self.trace[n + 2] if w2 else None)
+        self.kernel_launches += 1
+        if any(r >= 0 for ax in self.blk.nbr for r in ax):
+            self.plan.step_fixup(n + 1, out1, cur, out2, l2, self.trace_fix[n + 2] if w2 else None)
             self.kernel_launches += 1
-            if has_faces:
-                self.plan.step_fixup(n + 1, out1, cur, out2, l2, self.trace_fix[n + 2] if w2 else None)
-                self.kernel_launches += 1
-            n += 2
-            cur, prev = out2, out1
-        self.final_index = cur
+        self._cur, self._prev = out2, out1
+        self.final_index = out2
+        return n + 2
 
     def capture(self) -> None:
         """Capture steps 1..K into one CUDA graph (launch-bound at small blocks)."""
@@ -343,14 +353,14 @@ class StreamingSession:
     """
 
     H2D_BYTES_PER_STEP = 8
-    D2H_BYTES_PER_STEP = 16
+    D2H_BYTES_PER_STEP = 16 * _SLOTS
 
     def __init__(self, solver: FusedSolver):
         self.s = solver
         p = solver.p
         self.ct_host = torch.from_numpy(solver.ct.copy()).pin_memory()
         self.ct_dev = torch.zeros(p.K + 2, dtype=torch.float64, device=solver.device)
-        self.err_host = torch.zeros((p.K + 1, 2), dtype=torch.float64).pin_memory()
+        self.err_host = torch.zeros((p.K + 1, _SLOTS, 2), dtype=torch.float64).pin_memory()
         self._done: Dict[int, torch.cuda.Event] = {}
         solver.plan.set_ct_table(self.ct_dev)
 
@@ -371,20 +381,43 @@ class StreamingSession:
         return sum(t.numel() * 8 for t in self.s.tab)
 
     def step_async(self, n: int) -> None:
-        """Enqueue step n with its host input and the read-back of its result; do not wait."""
+        """Enqueue step n with its host input and the read-back of its result; do not wait.
+
+        In pair mode two steps travel together: the call for the first step of a pair only
+        uploads its input, the call for the second one launches the pass and reads both back."""
         s = self.s
         self.ct_dev[n: n + 1].copy_(self.ct_host[n: n + 1], non_blocking=True)
+        if s.pair:
+            if n == 1:
+                self._level = s.pair_begin(s.p.K)       # runs step 1 alone when K is odd
+                if self._level == 1:
+                    self._finish(1, 1)
+                    return
+            if n == self._level + 2:
+                self._level = s.pair_advance(self._level, force_err=True)
+                self._finish(n - 1, n)
+            return
         s.step(n, True)
-        self.err_host[n].copy_(s.trace[n], non_blocking=True)
+        self._finish(n, n)
+
+    def _finish(self, first: int, last: int) -> None:
+        self.err_host[first: last + 1].copy_(self.s.table[self.s.rank, first: last + 1], non_blocking=True)
         ev = torch.cuda.Event()
         ev.record()
-        self._done[n] = ev
+        for n in range(first, last + 1):
+            self._done[n] = ev
 
     def result(self, n: int) -> Tuple[float, float]:
         """(max error, sum of squares) of step n on this rank; waits for its read-back only."""
+        if n not in self._done:
+            raise RuntimeError(f"step {n} has not been launched yet (pair mode launches two steps at a time)")
         self._done.pop(n).synchronize()
-        return float(self.err_host[n, 0]), float(self.err_host[n, 1])
+        e = self.err_host[n]
+        return float(e[:, 0].max()), float(e[:, 1].sum())
 
     def step(self, n: int) -> Tuple[float, float]:
+        """Synchronous single step (not available in pair mode, where steps come in twos)."""
+        if self.s.pair:
+            raise RuntimeError("pair mode: use step_async(n) for consecutive n and result(n)")
         self.step_async(n)
         return self.result(n)

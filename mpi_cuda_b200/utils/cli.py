@@ -67,6 +67,7 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--report-every", type=int, default=2)
     ap.add_argument("--no-cfl-check", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch step kernels one by one instead of a CUDA graph")
+    ap.add_argument("--no-pair", action="store_true", help="fused backend: one pass per time step (no temporal blocking)")
     ap.add_argument("--variant", type=int, default=-1, help="TMA tile variant (see DESIGN.md)")
     ap.add_argument("--zchunk", type=int, default=0)
     ap.add_argument("--json", action="store_true")
@@ -154,7 +155,7 @@ def main(argv: Optional[List[str]] = None) -> int:
         res = solve(p, backend=args.backend, decomp=args.decomp, threads=args.threads,
                     every=args.report_every, ranks=args.ranks, verbose=not args.quiet,
                     check_cfl=not args.no_cfl_check, variant=args.variant, zchunk=args.zchunk,
-                    use_graph=not args.no_graph)
+                    use_graph=not args.no_graph, pair=not args.no_pair)
         if rank == 0:
             if not args.quiet:
                 print(phase_table(res))

@@ -246,6 +246,22 @@ def test_profile_steps_and_chrome_trace(tmp_path):
     assert len(json.load(open(out))["traceEvents"]) == 5
 
 
+@pytest.mark.parametrize("K", [6, 7])
+def test_streaming_session_in_pair_mode(K):
+    from mpi_cuda_b200.parallel.fused import FusedSolver, StreamingSession
+    p = WaveProblem(56, 2.0, 1e-3, K, bc="ddp")
+    base, _ = cpu.solve(p, every=1)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=True)
+    sess = StreamingSession(s)
+    sess.start()
+    for n in range(1, K + 1):
+        sess.step_async(n)
+    got = [sess.result(n) for n in range(1, K + 1)]
+    sess.close()
+    for (mx, s2), b in zip(got, base):
+        assert mx == b[2] and abs(math.sqrt(s2 / p.n_unknowns) - b[3]) <= 1e-12 * b[3]
+
+
 def test_golden_trace_512_on_gpu():
     """Published trace of the reference (report.pdf p.15-16 §4.3), on one B200."""
     from mpi_cuda_b200.parallel.fused import FusedSolver
