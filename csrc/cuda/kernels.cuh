@@ -176,8 +176,7 @@ __device__ __forceinline__ long long gidx(const Geometry& g, int i, int j, int k
 // Nodes are handled in batches of kShellBatch with all loads issued before any use:
 // the shell is latency-bound (scattered 8-byte accesses), so memory-level parallelism
 // per thread is what shortens the critical path in front of the flag release.
-constexpr int kShellBatch = 4;
-
+template <int kShellBatch>
 __device__ void shell_compute(const StepParams& P, long long first, long long stride, long long total,
                               bool push, double& mx, double& s2) {
   const Geometry& g = P.g;
@@ -527,8 +526,8 @@ fused_step_kernel(const __grid_constant__ StepParams P) {
 __global__ void __launch_bounds__(256) box_step_kernel(const __grid_constant__ StepParams P) {
   __shared__ double red[66];
   double mx = 0.0, s2 = 0.0;
-  shell_compute(P, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x,
-                P.boxes.prefix[P.boxes.nboxes], false, mx, s2);
+  shell_compute<4>(P, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x,
+                   P.boxes.prefix[P.boxes.nboxes], false, mx, s2);
   publish_error(P.err, mx, s2, red);
 }
 
@@ -536,7 +535,9 @@ __global__ void __launch_bounds__(256) box_step_kernel(const __grid_constant__ S
 // its second level once the neighbour's first-level edge has arrived.  One thread per node
 // over the shell boxes; acquires the flags for P.level, stores locally and into the
 // neighbours' ghost layers, and the last CTA releases P.level + 1.
-__global__ void __launch_bounds__(256) fixup_kernel(const __grid_constant__ StepParams P) {
+// One wave of 1024-thread CTAs (<= one per SM): a single flag wait, one batch of loads and one
+// system fence per CTA; with many small CTAs the per-CTA fence latency serialised over waves.
+__global__ void __launch_bounds__(1024, 1) fixup_kernel(const __grid_constant__ StepParams P) {
   __shared__ double red[66];
   double mx = 0.0, s2 = 0.0;
   if (P.use_flags) {
@@ -548,8 +549,8 @@ __global__ void __launch_bounds__(256) fixup_kernel(const __grid_constant__ Step
     }
     __syncthreads();
   }
-  shell_compute(P, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x,
-                P.boxes.prefix[P.boxes.nboxes], P.use_flags != 0, mx, s2);
+  shell_compute<2>(P, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x,
+                   P.boxes.prefix[P.boxes.nboxes], P.use_flags != 0, mx, s2);
   if (P.use_flags) {
     __syncthreads();
     if (threadIdx.x == 0) face_cta_done(P);

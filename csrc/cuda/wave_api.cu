@@ -666,9 +666,9 @@ int w3d_step_fixup(W3dPlan* p, int level, int cur, int prev, int out, double a, 
   P.flags_in = p->d.flags_in;
   P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
   P.level = (unsigned long long)level;     // waits for `level`, releases level + 1
-  const int blocks = (int)std::max<long long>(1, std::min<long long>((nodes + 1023) / 1024, (long long)p->num_sms * 4));
+  const int blocks = (int)std::max<long long>(1, std::min<long long>((nodes + 2047) / 2048, (long long)p->num_sms));
   P.n_face_ctas = blocks;
-  fixup_kernel<<<blocks, 256, 0, st>>>(P);
+  fixup_kernel<<<blocks, 1024, 0, st>>>(P);
   CUDA_TRY(cudaGetLastError());
   ++p->launches;
   return W3D_OK;
