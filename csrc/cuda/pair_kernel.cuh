@@ -32,8 +32,9 @@
 
 namespace w3d {
 
-template <int TX, int RPT, int RG, int STAGES>
+template <int TX, int RPT, int RG, int STAGES, int MINB = 1>
 struct PairCfg {
+  static constexpr int kMinBlocks = MINB;                  // CTAs per SM the launch bounds ask for
   static constexpr int kTX = TX, kRPT = RPT, kRG = RG, kStages = STAGES;
   static constexpr int kTY = RPT * RG;
   static constexpr int kWA = TX + 4, kRowsA = kTY + 4;     // u^n box (two ghost layers)
@@ -278,7 +279,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
 }
 
 template <class Cfg>
-__global__ void __launch_bounds__(Cfg::kThreads, 1) pair_step_kernel(const __grid_constant__ PairParams P) {
+__global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kernel(const __grid_constant__ PairParams P) {
   constexpr int TX = Cfg::kTX, STAGES = Cfg::kStages;
   // Indexed directly (no integer round trip) so the compiler keeps the shared address space:
   // LDS/STS with 32-bit addresses instead of generic LD/ST with 64-bit address arithmetic.

@@ -66,19 +66,23 @@ using PCfg1 = PairCfg<64, 8, 4, 3>;    // 3-stage ring (~150 KB)
 using PCfg2 = PairCfg<128, 8, 4, 2>;   // 128 x 32 tile, 544 threads, 2-stage ring (~215 KB)
 using PCfg3 = PairCfg<64, 4, 8, 4>;    // 64 x 32 tile, 4 rows per thread: 544 threads (16 consumer warps)
 using PCfg4 = PairCfg<64, 4, 8, 3>;
-using PCfg5 = PairCfg<64, 2, 15, 4>;   // 64 x 30 tile, 2 rows per thread: 992 threads (30 consumer warps)
+using PCfg5 = PairCfg<64, 2, 15, 4>;   // 64 x 30 tile, 2 rows per thread: 960 threads (30 warps)
+using PCfg6 = PairCfg<64, 4, 4, 3, 2>; // 64 x 16 tile, 256 threads, ~88 KB: TWO CTAs per SM (small blocks)
+using PCfg7 = PairCfg<64, 4, 4, 4, 2>; // same with a 4-stage ring (~108 KB)
 struct PairVariant {
-  int tx, ty, threads, smem;
+  int tx, ty, threads, smem, ctas_per_sm;
   void (*kernel)(const PairParams);
   const char* name;
 };
 const PairVariant kPairVariants[] = {
-    {PCfg0::kTX, PCfg0::kTY, PCfg0::kThreads, PCfg0::kSmemBytes, pair_step_kernel<PCfg0>, "pair 64x32x4st"},
-    {PCfg1::kTX, PCfg1::kTY, PCfg1::kThreads, PCfg1::kSmemBytes, pair_step_kernel<PCfg1>, "pair 64x32x3st"},
-    {PCfg2::kTX, PCfg2::kTY, PCfg2::kThreads, PCfg2::kSmemBytes, pair_step_kernel<PCfg2>, "pair 128x32x2st"},
-    {PCfg3::kTX, PCfg3::kTY, PCfg3::kThreads, PCfg3::kSmemBytes, pair_step_kernel<PCfg3>, "pair 64x32x4st rpt4"},
-    {PCfg4::kTX, PCfg4::kTY, PCfg4::kThreads, PCfg4::kSmemBytes, pair_step_kernel<PCfg4>, "pair 64x32x3st rpt4"},
-    {PCfg5::kTX, PCfg5::kTY, PCfg5::kThreads, PCfg5::kSmemBytes, pair_step_kernel<PCfg5>, "pair 64x30x4st rpt2"},
+    {PCfg0::kTX, PCfg0::kTY, PCfg0::kThreads, PCfg0::kSmemBytes, 1, pair_step_kernel<PCfg0>, "pair 64x32x4st"},
+    {PCfg1::kTX, PCfg1::kTY, PCfg1::kThreads, PCfg1::kSmemBytes, 1, pair_step_kernel<PCfg1>, "pair 64x32x3st"},
+    {PCfg2::kTX, PCfg2::kTY, PCfg2::kThreads, PCfg2::kSmemBytes, 1, pair_step_kernel<PCfg2>, "pair 128x32x2st"},
+    {PCfg3::kTX, PCfg3::kTY, PCfg3::kThreads, PCfg3::kSmemBytes, 1, pair_step_kernel<PCfg3>, "pair 64x32x4st rpt4"},
+    {PCfg4::kTX, PCfg4::kTY, PCfg4::kThreads, PCfg4::kSmemBytes, 1, pair_step_kernel<PCfg4>, "pair 64x32x3st rpt4"},
+    {PCfg5::kTX, PCfg5::kTY, PCfg5::kThreads, PCfg5::kSmemBytes, 1, pair_step_kernel<PCfg5>, "pair 64x30x4st rpt2"},
+    {PCfg6::kTX, PCfg6::kTY, PCfg6::kThreads, PCfg6::kSmemBytes, 2, pair_step_kernel<PCfg6>, "pair 64x16x3st rpt4 2cta"},
+    {PCfg7::kTX, PCfg7::kTY, PCfg7::kThreads, PCfg7::kSmemBytes, 2, pair_step_kernel<PCfg7>, "pair 64x16x4st rpt4 2cta"},
 };
 constexpr int kNumPairVariants = sizeof(kPairVariants) / sizeof(kPairVariants[0]);
 constexpr int kDefaultVariant = 3;   // best of the measured sweep at 512^3 (profiles/variant_sweep.md)
@@ -524,7 +528,8 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const*
       if (zc + 4 > 640) continue;                 // the kernel stages zc+4 table entries in shared memory
       const long long ctas = tiles * ((ez + zc - 1) / zc);
       if (ctas > W3D_MAX_PARTIALS) break;
-      const long long waves = (ctas + p->num_sms - 1) / p->num_sms;
+      const long long slots = (long long)p->num_sms * v.ctas_per_sm;
+      const long long waves = (ctas + slots - 1) / slots;
       const double cost = (double)waves * (zc + 4.0 * 0.45 + 2.0);
       if (cost < best - 1e-9) { best = cost; best_c = c; }
     }

@@ -296,7 +296,7 @@ def test_native_mpigpu_executable_matches_python_path():
     assert len(got) == 5 and abs(got[-1][2] - base[-1][2]) <= 1e-6 * base[-1][2]
 
 
-@pytest.mark.parametrize("pair_variant", [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize("pair_variant", [0, 1, 2, 3, 4, 5, 6, 7])
 @pytest.mark.parametrize("N,K", [((70, 45, 37), 6), ((130, 66, 50), 7), ((257, 40, 23), 4)])
 def test_pair_kernel_bit_exact_vs_cpu(N, K, pair_variant):
     """Temporal blocking (two steps per pass) must give exactly the fields of K single steps."""
