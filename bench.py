@@ -107,7 +107,7 @@ def main() -> int:
     ap.add_argument("--tau", type=float, default=1e-3)
     ap.add_argument("--bc", default="ddd")
     ap.add_argument("--backend", default="fused", choices=("fused", "nccl"))
-    ap.add_argument("--decomp", default="block")
+    ap.add_argument("--decomp", default="auto", help="auto | slab | block | PxQxR")
     ap.add_argument("--variant", type=int, default=-1)
     ap.add_argument("--zchunk", type=int, default=0)
     ap.add_argument("--reps", type=int, default=7)
@@ -143,7 +143,7 @@ def main() -> int:
     p = WaveProblem(Ns if len(Ns) == 3 else Ns[0], Ls if len(Ls) == 3 else Ls[0], args.tau, K, bc=args.bc)
     grid_name = "%dx%dx%d" % p.N if len(set(p.N)) > 1 else "%d^3" % p.N[0]
     p.check_cfl()
-    dims = parse_dims(args.decomp, world)
+    dims = parse_dims(args.decomp, world, p.unknowns)
 
     def barrier():
         torch.cuda.synchronize(device)

@@ -50,9 +50,20 @@ def default_dims(world: int, kind: str = "block") -> Tuple[int, int, int]:
     return tuple(dims)
 
 
-def parse_dims(spec: str, world: int) -> Tuple[int, int, int]:
-    """'slab' | 'block' | 'PxQxR' (x, y, z order)."""
+def auto_dims(world: int, unknowns: Sequence[int]) -> Tuple[int, int, int]:
+    """Measured policy (profiles/scaling.md): slabs while they stay at least 48 planes thick on a
+    grid of at most 768 nodes per axis (latency-bound regime: two contiguous z faces beat a y face
+    plus z faces by ~4 % at 512^3 on 8 GPUs); 3-D blocks otherwise (less halo volume, 1024^3+)."""
+    if world > 1 and max(unknowns) <= 768 and unknowns[2] // world >= 48:
+        return default_dims(world, "slab")
+    return default_dims(world, "block")
+
+
+def parse_dims(spec: str, world: int, unknowns: Optional[Sequence[int]] = None) -> Tuple[int, int, int]:
+    """'slab' | 'block' | 'auto' | 'PxQxR' (x, y, z order)."""
     s = spec.lower()
+    if s == "auto":
+        return auto_dims(world, unknowns) if unknowns is not None else default_dims(world, "block")
     if s in ("slab", "block"):
         return default_dims(world, s)
     parts = [int(t) for t in s.replace("*", "x").split("x")]

@@ -88,3 +88,11 @@ def test_gloo_rank_count_invariance(world, dims, bc):
             assert a[2] == b[2]
             assert abs(a[3] - b[3]) <= 1e-13 * b[3]
         assert phases["exchange"] > 0
+
+
+def test_auto_decomposition_policy():
+    assert decomp.parse_dims("auto", 8, (511, 511, 511)) == (1, 1, 8)      # 63 planes per rank: slab
+    assert decomp.parse_dims("auto", 8, (1023, 1023, 1023)) == (1, 2, 4)   # large grid: blocks
+    assert decomp.parse_dims("auto", 8, (255, 255, 255)) == (1, 2, 4)      # slabs would be too thin
+    assert decomp.parse_dims("auto", 1, (511, 511, 511)) == (1, 1, 1)
+    assert decomp.parse_dims("auto", 4) == (1, 2, 2)
