@@ -33,7 +33,7 @@ def _world() -> int:
 
 def resolve_dims(p: WaveProblem, decomp: str, world: int):
     from ..parallel.decomp import parse_dims
-    return parse_dims(decomp, world)
+    return parse_dims(decomp, world, p.unknowns)
 
 
 def solve(p: WaveProblem, backend: str = "auto", decomp: str = "block", threads: int = 1, every: int = 2,

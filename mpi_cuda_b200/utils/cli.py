@@ -61,7 +61,7 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--bc", default="ddd", help="per-axis boundary: d (Dirichlet) or p (periodic), e.g. ddp")
     ap.add_argument("--backend", default="auto",
                     choices=("auto", "fused", "nccl", "gloo", "cpu", "cpu-omp", "cpu-ranks", "torch"))
-    ap.add_argument("--decomp", default="block", help="slab | block | PxQxR")
+    ap.add_argument("--decomp", default="block", help="auto | slab | block | PxQxR")
     ap.add_argument("--ranks", type=int, default=1, help="in-process ranks for --backend cpu-ranks")
     ap.add_argument("--threads", type=int, default=None, help="OpenMP threads per rank")
     ap.add_argument("--report-every", type=int, default=2)
@@ -102,7 +102,7 @@ def _fused_session(p: WaveProblem, args, rank: int) -> int:
     from ..utils.timing import write_chrome_trace
     p.check_cfl(strict=not args.no_cfl_check)
     world = dist.get_world_size() if dist.is_initialized() else 1
-    s = FusedSolver(p, parse_dims(args.decomp, world), every=args.report_every, variant=args.variant,
+    s = FusedSolver(p, parse_dims(args.decomp, world, p.unknowns), every=args.report_every, variant=args.variant,
                     zchunk=args.zchunk, use_graph=False)
     if args.trace:
         ms = s.profile_steps()
