@@ -339,3 +339,20 @@ def test_pair_kernel_golden_trace_and_graph():
     res = s.run()
     for (n, t, mx, l2), (gn, gt, gmx, gl2) in zip(res.trace, report.GOLDEN_512):
         assert n == gn and abs(mx - gmx) <= 5e-15 and abs(l2 - gl2) <= 1e-6 * gl2
+
+
+@pytest.mark.parametrize("N,K,bc", [((9, 7, 5), 3, "ddd"), ((65, 33, 6), 4, "ddp"), ((12, 70, 9), 1, "ppp"),
+                                    ((4, 4, 4), 2, "ddd"), ((200, 9, 140), 5, "dpd")])
+@pytest.mark.parametrize("pair", [False, True])
+def test_small_and_odd_blocks(N, K, bc, pair):
+    """Blocks smaller than a tile, one-plane-thin chunks, K = 1, every axis periodic."""
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem(N, 3.0, 1e-3, K, bc=bc)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=pair)
+    res = s.run()
+    s.check_status()
+    ref, _, _ = _cpu_fields(p, K)
+    assert np.array_equal(s.final_field().cpu().numpy(), ref[K])
+    base, _ = cpu.solve(p, every=1)
+    for a, c in zip(res.trace, base):
+        assert a[2] == c[2] and abs(a[3] - c[3]) <= 1e-12 * max(c[3], 1e-300)
