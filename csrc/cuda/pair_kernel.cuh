@@ -128,6 +128,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
   const bool want1 = P.err1.out != nullptr, want2 = P.err2.out != nullptr;
   const double ct1 = P.ct_ptr ? __ldg(P.ct_ptr) : P.ct1, ct2 = P.ct_ptr ? __ldg(P.ct_ptr + 1) : P.ct2;
   double acc1[RPT], zA[RPT], acc2[RPT], zL[RPT], sxy[RPT];
+  double zA1[RPT], zL1[RPT];            // second register set of the z pipeline (see `iter`)
   bool in1[RPT], st1[RPT], st2[RPT];
   const double sxv = x_in ? P.sx[gx] : 0.0;
 #pragma unroll
@@ -142,7 +143,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
     st2[r] = st1[r] && (XFULL || (!(P.skip_lo[0] && gx == 1) && !(P.skip_hi[0] && gx == g.n[0]))) &&
              (FULL || (!(P.skip_lo[1] && gy == 1) && !(P.skip_hi[1] && gy == g.n[1])));
     sxy[r] = in1[r] ? sxv * P.sy[min(max(gy, 0), g.n[1] + 1)] : 0.0;
-    acc1[r] = zA[r] = acc2[r] = zL[r] = 0.0;
+    acc1[r] = zA[r] = acc2[r] = zL[r] = zA1[r] = zL1[r] = 0.0;
   }
   // ring node of this thread (level 1 only), in level-1-plane coordinates
   const bool has_ring = tid < Cfg::kRing;
@@ -164,7 +165,10 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
   const int off1 = (r0 + 1) * W1 + cxi + 1;      // level-1 plane: tile node (cxi, r0)
   const int offRA = (rry + 1) * WA + rcx + 1, offRB = rry * WB + rcx + 1, offR1 = rry * W1 + rcx;
 
-  for (int t = 0; t < iters; ++t) {
+  // One plane.  zAp/zLp hold u^n / level 1 of the previous plane (own column), zAc/zLc receive
+  // those of the current plane; the caller alternates the two register sets, so the z pipeline
+  // advances without any register-to-register copies.
+  auto iter = [&](const int t, double (&zAp)[RPT], double (&zLp)[RPT], double (&zAc)[RPT], double (&zLc)[RPT]) {
     const int s = t % STAGES;
     const uint32_t ph = (uint32_t)(t / STAGES) & 1u;
     const int p = z0 - 2 + t;                 // plane of u^n that has just arrived
@@ -173,36 +177,36 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
     const double* Bs = reinterpret_cast<const double*>(stage0 + (size_t)s * Cfg::kStageBytes + Cfg::kABytes);
     double* L1w = l1buf + (size_t)((t + 1) & 1) * (Cfg::kL1Bytes / 8);     // plane p-1 of level 1
     // ---- level 1 ----
-    double colA[RPT + 2];
+    const double aTop = As[offA];                         // row above this thread's rows
+    const double aBot = As[offA + (RPT + 1) * WA];        // row below
 #pragma unroll
-    for (int q = 0; q < RPT + 2; ++q) colA[q] = As[offA + q * WA];
+    for (int r = 0; r < RPT; ++r) zAc[r] = As[offA + (r + 1) * WA];
     const int p1 = p - 1;                                        // level-1 plane completed now
     const bool p1_live = t >= 2 && p1 >= 1 && p1 <= g.n[2];     // otherwise level 1 is 0 there
     const bool p1_store = p1 >= z0 && p1 < z1;
     const bool p_l1 = p >= z0 - 1 && p <= z1;                   // plane p needs a level-1 partial
-    double l1c[RPT];
 #pragma unroll
-    for (int r = 0; r < RPT; ++r) l1c[r] = w3d_finish(acc1[r], colA[r + 1], P.c1z);
+    for (int r = 0; r < RPT; ++r) zLc[r] = w3d_finish(acc1[r], zAc[r], P.c1z);
     if (!p1_live) {
 #pragma unroll
-      for (int r = 0; r < RPT; ++r) l1c[r] = 0.0;
+      for (int r = 0; r < RPT; ++r) zLc[r] = 0.0;
     } else if (!(FULL && XFULL)) {
 #pragma unroll
-      for (int r = 0; r < RPT; ++r) l1c[r] = in1[r] ? l1c[r] : 0.0;
+      for (int r = 0; r < RPT; ++r) zLc[r] = in1[r] ? zLc[r] : 0.0;
     }
 #pragma unroll
-    for (int r = 0; r < RPT; ++r) L1w[off1 + r * W1] = l1c[r];
+    for (int r = 0; r < RPT; ++r) L1w[off1 + r * W1] = zLc[r];
     if (p1_store) {
       double* o = o1 + (long long)p1 * g.plane;
 #pragma unroll
       for (int r = 0; r < RPT; ++r)
-        if (st1[r]) o[r * pitch] = l1c[r];
+        if (st1[r]) o[r * pitch] = zLc[r];
       if (want1) {
         const double szt = s_sz[t - 1] * ct1;      // s_sz[i] = sz[z0 - 2 + i]
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
           if (st1[r]) {
-            const double e = w3d_abs_err(l1c[r], sxy[r], szt);
+            const double e = w3d_abs_err(zLc[r], sxy[r], szt);
             mx1 = fmax(mx1, e);
             s21 = fma(e, e, s21);
           }
@@ -222,8 +226,9 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
         const double xm = As[offA + (r + 1) * WA - 1];
         const double xp = As[offA + (r + 1) * WA + 1];
         const double pv = Bs[offB + r * WB];
-        acc1[r] = w3d_partial(colA[r + 1], pv, xm, xp, colA[r], colA[r + 2], zA[r], P.a1, P.b1, P.c1x, P.c1y,
-                              P.c1z);
+        const double ym = r == 0 ? aTop : zAc[r - 1];
+        const double yp = r == RPT - 1 ? aBot : zAc[r + 1];
+        acc1[r] = w3d_partial(zAc[r], pv, xm, xp, ym, yp, zAp[r], P.a1, P.b1, P.c1x, P.c1y, P.c1z);
       }
       if (has_ring) {
         const double* a = As + offRA;
@@ -239,7 +244,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
       const bool skipz = (P.skip_lo[2] && p2 == 1) || (P.skip_hi[2] && p2 == g.n[2]);
       double v2[RPT];
 #pragma unroll
-      for (int r = 0; r < RPT; ++r) v2[r] = w3d_finish(acc2[r], l1c[r], P.c2z);
+      for (int r = 0; r < RPT; ++r) v2[r] = w3d_finish(acc2[r], zLc[r], P.c2z);
       if (!skipz) {
         double* o = o2 + (long long)p2 * g.plane;
 #pragma unroll
@@ -265,16 +270,15 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
       for (int r = 0; r < RPT; ++r) {
         const double xm = L1w[off1 + r * W1 - 1];
         const double xp = L1w[off1 + r * W1 + 1];
-        const double ym = r == 0 ? ym0 : l1c[r - 1];
-        const double yp = r == RPT - 1 ? ypN : l1c[r + 1];
-        acc2[r] = w3d_partial(l1c[r], zA[r], xm, xp, ym, yp, zL[r], P.a2, P.b2, P.c2x, P.c2y, P.c2z);
+        const double ym = r == 0 ? ym0 : zLc[r - 1];
+        const double yp = r == RPT - 1 ? ypN : zLc[r + 1];
+        acc2[r] = w3d_partial(zLc[r], zAp[r], xm, xp, ym, yp, zLp[r], P.a2, P.b2, P.c2x, P.c2y, P.c2z);
       }
     }
-#pragma unroll
-    for (int r = 0; r < RPT; ++r) {
-      zL[r] = l1c[r];
-      zA[r] = colA[r + 1];
-    }
+  };
+  for (int t = 0; t < iters; t += 2) {
+    iter(t, zA, zL, zA1, zL1);
+    if (t + 1 < iters) iter(t + 1, zA1, zL1, zA, zL);
   }
 }
 
