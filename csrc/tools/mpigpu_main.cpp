@@ -7,7 +7,8 @@
 // step kernel pushes halos over NVLink itself — there is no MPI in this program.
 //
 //   mpigpu [-np G] N tau K [threads] [--L L | --Lpi] [--bc ddd] [--variant v] [--zchunk z]
-//          [--every n] [--quiet] [--kernel fused|tma|box]
+//          [--every n] [--quiet] [--kernel pair|fused|tma|box]
+// --kernel pair (default): two time steps per pass + fix-up pass; fused: one pass per step.
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -46,7 +47,7 @@ struct Opts {
   int N = 512, K = 20, G = 1, variant = -1, zchunk = 0, every = 2, verbose = 1;
   double tau = 1e-3, L = 1.0;
   int periodic[3] = {0, 0, 0};
-  std::string kernel = "fused";
+  std::string kernel = "pair";
 };
 
 struct HostBarrier {
@@ -64,6 +65,8 @@ struct Rank {
   int dev = 0, lo = 0, n[3] = {0, 0, 0};
   W3dBlock blk;
   double* field[2] = {nullptr, nullptr};
+  double* aux[2] = {nullptr, nullptr};      // two more arrays for the two-steps-per-pass kernel
+  bool faces = false;                       // any face with a neighbour (other GPU or periodic wrap)
   unsigned long long* flags = nullptr;
   double* tab[3] = {nullptr, nullptr, nullptr};
   uint32_t* status = nullptr;
@@ -129,10 +132,11 @@ int main(int argc, char** argv) {
     k.blk.xoff = W3D_XOFF; k.blk.pitch = w3d_pitch_for(k.n[0]);
     const size_t elems = (size_t)(k.n[2] + 2) * (k.n[1] + 2) * k.blk.pitch;
     for (int f = 0; f < 2; ++f) CK(cudaMalloc(&k.field[f], elems * sizeof(double)));
+    for (int f = 0; f < 2; ++f) { CK(cudaMalloc(&k.aux[f], elems * sizeof(double))); CK(cudaMemset(k.aux[f], 0, elems * sizeof(double))); }
     CK(cudaMalloc(&k.flags, 64)); CK(cudaMemset(k.flags, 0, 64));
     CK(cudaMalloc(&k.status, 16)); CK(cudaMemset(k.status, 0, 16));
     CK(cudaMalloc(&k.ws, w3d_workspace_bytes())); CK(cudaMemset(k.ws, 0, w3d_workspace_bytes()));
-    CK(cudaMalloc(&k.trace, sizeof(double) * 2 * (K + 1))); CK(cudaMemset(k.trace, 0, sizeof(double) * 2 * (K + 1)));
+    CK(cudaMalloc(&k.trace, sizeof(double) * 4 * (K + 1))); CK(cudaMemset(k.trace, 0, sizeof(double) * 4 * (K + 1)));   // 2 slots x (max, sum)
     for (int d = 0; d < 3; ++d) {
       const int lo = d == 2 ? first[2] + k.lo : first[d];
       std::vector<double> t(k.n[d] + 2);
@@ -185,7 +189,18 @@ int main(int argc, char** argv) {
     if (hi_n < G) set_peer(5, R[hi_n], 0, 4);
     d.flags_in = k.flags; d.status = k.status; d.workspace = k.ws; d.workspace_bytes = w3d_workspace_bytes();
     d.variant = o.variant; d.zchunk = o.zchunk; d.num_sms = 0; d.spin_timeout_ms = 0;
+    for (int f = 0; f < 6; ++f) k.faces = k.faces || d.peer[f].active;
     W3(w3d_plan_create(&d, &k.plan));
+    if (o.kernel == "pair") {
+      double* peer_aux[12] = {nullptr};
+      for (int f = 0; f < 6; ++f)
+        if (d.peer[f].active) {
+          // find the rank that owns this peer's field[0]
+          for (int q = 0; q < G; ++q)
+            if (R[q].field[0] == d.peer[f].field[0]) { peer_aux[2 * f] = R[q].aux[0]; peer_aux[2 * f + 1] = R[q].aux[1]; }
+        }
+      W3(w3d_plan_enable_pairs(k.plan, k.aux[0], k.aux[1], peer_aux, o.variant, o.zchunk));
+    }
     if (o.verbose && r == 0) std::printf("plan: %s\n", w3d_plan_describe(k.plan));
   }
   // ---- run: one host thread per GPU ----
@@ -206,10 +221,26 @@ int main(int argc, char** argv) {
       CK(cudaStreamSynchronize(st));
       bar.wait();
       CK(cudaEventRecord(e1, st));
-      for (int n = 1; n <= K; ++n) {
+      auto coef = [](int n, double* a, double* b, double* cs) { *a = n == 1 ? 1.0 : 2.0; *b = n == 1 ? 0.0 : -1.0; *cs = n == 1 ? 0.5 : 1.0; };
+      auto slot = [&](int n, int q) -> double* { return (n % o.every == 0) ? k.trace + 4 * n + 2 * q : nullptr; };
+      if (o.kernel == "pair") {
+        // array roles rotate over the four arrays: (0,1)->(2,3), (3,2)->(0,1), (1,0)->(2,3), ...
+        int n = 0, cur = 0, prev = 1;
+        double a1, b1, c1, a2, b2, c2;
+        if (K % 2 == 1) { coef(1, &a1, &b1, &c1); W3(w3d_step_fused(k.plan, 0, a1, b1, c1, ct[1], slot(1, 0), st)); n = 1; cur = 1; prev = 0; }
+        const bool faces = k.faces;
+        while (n < K) {
+          const int o1 = cur <= 1 ? 2 : 0, o2 = cur <= 1 ? 3 : 1;
+          coef(n + 1, &a1, &b1, &c1); coef(n + 2, &a2, &b2, &c2);
+          W3(w3d_step_pair(k.plan, n, cur, prev, o1, o2, a1, b1, c1, ct[n + 1], a2, b2, c2, ct[n + 2], slot(n + 1, 0), slot(n + 2, 0), st));
+          if (faces) W3(w3d_step_fixup(k.plan, n + 1, o1, cur, o2, a2, b2, c2, ct[n + 2], slot(n + 2, 1), st));
+          n += 2; cur = o2; prev = o1;
+        }
+      }
+      for (int n = 1; n <= K && o.kernel != "pair"; ++n) {
         const int s = n - 1;
         const double a = n == 1 ? 1.0 : 2.0, b = n == 1 ? 0.0 : -1.0, cs = n == 1 ? 0.5 : 1.0;
-        double* err = (n % o.every == 0) ? k.trace + 2 * n : nullptr;
+        double* err = slot(n, 0);
         if (o.kernel == "fused") W3(w3d_step_fused(k.plan, s, a, b, cs, ct[n], err, st));
         else if (o.kernel == "tma") W3(w3d_step_tma(k.plan, s, a, b, cs, ct[n], nullptr, nullptr, err, 0, st));
         else W3(w3d_step_box(k.plan, s, a, b, cs, ct[n], nullptr, nullptr, err, 0, st));
@@ -220,13 +251,13 @@ int main(int argc, char** argv) {
     }
     CK(cudaEventElapsedTime(&k.init_ms, e0, e1));
     CK(cudaEventElapsedTime(&k.loop_ms, e1, e2));
-    k.htrace.resize(2 * (K + 1));
-    CK(cudaMemcpy(k.htrace.data(), k.trace, sizeof(double) * 2 * (K + 1), cudaMemcpyDeviceToHost));
+    k.htrace.resize(4 * (K + 1));
+    CK(cudaMemcpy(k.htrace.data(), k.trace, sizeof(double) * 4 * (K + 1), cudaMemcpyDeviceToHost));
     uint32_t stt = 0;
     CK(cudaMemcpy(&stt, k.status, 4, cudaMemcpyDeviceToHost));
     if (stt) std::fprintf(stderr, "GPU %d: watchdog status 0x%x\n", r, stt);
   };
-  if ((o.kernel != "fused") && (G > 1 || o.periodic[0] || o.periodic[1] || o.periodic[2])) {
+  if ((o.kernel != "fused" && o.kernel != "pair") && (G > 1 || o.periodic[0] || o.periodic[1] || o.periodic[2])) {
     std::fprintf(stderr, "--kernel %s has no halo exchange: single GPU, Dirichlet only\n", o.kernel.c_str());
     return 2;
   }
@@ -238,7 +269,8 @@ int main(int argc, char** argv) {
   for (int n = 1; n <= K; ++n) {
     if (n % o.every) continue;
     double mx = 0, s2 = 0;
-    for (int r = 0; r < G; ++r) { mx = std::max(mx, R[r].htrace[2 * n]); s2 += R[r].htrace[2 * n + 1]; }
+    for (int r = 0; r < G; ++r)
+      for (int q = 0; q < 2; ++q) { mx = std::max(mx, R[r].htrace[4 * n + 2 * q]); s2 += R[r].htrace[4 * n + 2 * q + 1]; }
     if (o.verbose) std::printf("Step %d, t = %.6f, Max Error = %.6e, L2 Error = %.6e\n", n, n * o.tau, mx, std::sqrt(s2 / cnt));
   }
   float loop = 0, init = 0;
