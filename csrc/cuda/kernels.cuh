@@ -20,7 +20,9 @@
 //                   releases the flags for the next level (st.release.sys).  The
 //                   remaining CTAs stream the interior while those stores fly.
 //  * `shell_compute` — one-thread-per-node path over a box list; used by the
-//                   plain `box_step_kernel` (NCCL baseline's thin boxes, numerics checks).
+//                   plain `box_step_kernel` (NCCL baseline's thin boxes, numerics checks)
+//                   and by `fixup_kernel`, the second launch of the two-steps-per-pass
+//                   scheme (pair_kernel.cuh), which also ships halos and releases flags.
 #pragma once
 #include "ptx.cuh"
 #include "stencil_core.h"

@@ -36,13 +36,13 @@ int fail(int code, const char* fmt, ...) {
   } while (0)
 
 // ---- TMA tile variants ------------------------------------------------------------
-//            TX  RPT RG STAGES   (+32 producer threads, +128 shell threads per CTA)
-using Cfg0 = TileCfg<128, 8, 1, 4>;   // 128 x 8 tile,  288 threads, ~76 KB  -> 2 CTAs / SM
-using Cfg1 = TileCfg<128, 8, 2, 4>;   // 128 x 16 tile, 416 threads, ~143 KB -> 1 CTA / SM
-using Cfg2 = TileCfg<128, 8, 4, 3>;   // 128 x 32 tile, 672 threads, ~207 KB -> 1 CTA / SM
-using Cfg3 = TileCfg<64, 8, 4, 4>;    // 64 x 32 tile,  416 threads, ~141 KB -> 1 CTA / SM  (default)
+//            TX  RPT RG STAGES   (+32 threads: the producer warp)
+using Cfg0 = TileCfg<128, 8, 1, 4>;   // 128 x 8 tile,  160 threads, ~76 KB  -> 2 CTAs / SM
+using Cfg1 = TileCfg<128, 8, 2, 4>;   // 128 x 16 tile, 288 threads, ~143 KB -> 1 CTA / SM
+using Cfg2 = TileCfg<128, 8, 4, 3>;   // 128 x 32 tile, 544 threads, ~207 KB -> 1 CTA / SM
+using Cfg3 = TileCfg<64, 8, 4, 4>;    // 64 x 32 tile,  288 threads, ~141 KB -> 1 CTA / SM  (default)
 using Cfg4 = TileCfg<64, 8, 4, 5>;    // 64 x 32 tile,  5-stage ring, ~176 KB -> 1 CTA / SM
-using Cfg5 = TileCfg<64, 8, 2, 6>;    // 64 x 16 tile,  288 threads, ~109 KB -> 2 CTAs / SM
+using Cfg5 = TileCfg<64, 8, 2, 6>;    // 64 x 16 tile,  160 threads, ~109 KB -> 2 CTAs / SM
 
 struct Variant {
   int tx, ty, threads, smem, ctas_per_sm;

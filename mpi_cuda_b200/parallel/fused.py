@@ -1,19 +1,24 @@
-"""Fused multi-GPU solver: one kernel per time step, halo exchange inside it.
+"""Fused multi-GPU solver: the halo exchange and the error reduction live inside the step kernels.
 
 This is the product path (BASELINE.json north star).  Where the reference's
 MPI+CUDA program staged halos D2H -> MPI_Sendrecv -> H2D every step (separate
 "H2D/D2H" and "MPI" columns in report.pdf p.16 §4.4) and reduced the error with
 MPI, here:
 
-  * every rank's two field arrays and its flag words live in symmetric memory
-    (``torch.distributed._symmetric_memory``), so a kernel on GPU A can store to
-    GPU B's arrays over NVLink 5 / NVSwitch;
-  * ``w3d_step_fused`` computes the shell first, stores it locally and into the
-    neighbours' ghost layers, and releases a system-scope flag; the neighbours'
-    shell CTAs acquire that flag before their next step — no host, no NCCL;
-  * the error max / sum-of-squares is an epilogue of the same kernel; the only
-    collective left is one tiny all-gather of the per-step scalars *after* the
-    time loop.
+  * every rank's field arrays, its flag words and its error table live in
+    symmetric memory (``torch.distributed._symmetric_memory``), so a kernel on
+    GPU A can store to GPU B's arrays over NVLink 5 / NVSwitch;
+  * the step kernels number the CTAs that touch a face with a neighbour first;
+    those acquire the neighbour's flag before loading, and after their tile is
+    written they copy its face layers straight into the neighbour's ghost layers
+    and release a system-scope flag — no host, no NCCL inside the time loop;
+  * the error max / sum-of-squares is an epilogue of the same kernels, and the
+    last CTA stores the pair into every rank's table, so after the loop each rank
+    already holds all partials (no collective at all);
+  * by default two time steps share one pass over memory (``pair=True``:
+    ``w3d_step_pair`` + ``w3d_step_fixup``); ``pair=False`` runs
+    one ``w3d_step_fused`` launch per step;
+  * the K steps of a run are captured in one CUDA graph.
 
 With world size 1 the same code runs on plain device tensors (a periodic axis
 wraps onto the rank itself through the same peer mechanism).

@@ -151,11 +151,28 @@ def test_pack_unpack_matches_cpu():
             ops.plan.pack_face(0, axis, side, buf, ghost=False)
             want = cpu.pack(host.numpy(), b, axis, side, ghost=False)
             assert np.array_equal(buf.cpu().numpy(), want)
+            ops.f[1].zero_()
             ops.plan.unpack_face(1, axis, side, buf, ghost=True)
-            chk = np.zeros(host.shape); cpu.unpack(chk, b, axis, side, want, ghost=True)
-            f1 = ops.f[1].cpu().numpy()
-            assert np.array_equal(f1 != 0, chk != 0) or np.array_equal(f1[chk != 0], chk[chk != 0])
-    assert True
+            chk = np.zeros(host.shape)
+            cpu.unpack(chk, b, axis, side, want, ghost=True)
+            assert np.array_equal(ops.f[1].cpu().numpy(), chk)     # exactly the ghost layer, nothing else
+
+
+def test_wrap_axis_matches_cpu():
+    p = WaveProblem((13, 11, 7), 1.0, 1e-3, 1)
+    ops, blk = _cuda_ops(p)
+    from mpi_cuda_b200.ops.cuda import XOFF, pitch_for
+    b = cpu.make_block(blk.n, xoff=XOFF, pitch=pitch_for(blk.n[0]))
+    g = torch.Generator().manual_seed(5)
+    for axis in range(3):
+        host = torch.randn(ops.f[0].shape, dtype=torch.float64, generator=g)
+        ops.f[0].copy_(host)
+        ops.plan.wrap_axis(0, axis)
+        want = host.numpy().copy()
+        cpu.wrap(want, b, axis)
+        got = ops.f[0].cpu().numpy()
+        xs = slice(XOFF, XOFF + blk.n[0] + 2)
+        assert np.array_equal(got[:, :, xs], want[:, :, xs])
 
 
 @pytest.mark.parametrize("bc", ["ddp", "ppp", "pdd"])

@@ -130,3 +130,17 @@ def test_cli_parses_session_flags():
     assert args.checkpoint == "/tmp/x" and args.checkpoint_at == 10 and p.bc == "ddp"
     p, args = parse(["1024", "pi", "0.1", "100", "--decomp", "1x2x4", "--backend", "fused"])
     assert p.K == 100 and abs(p.tau - 1e-3) < 1e-15 and args.decomp == "1x2x4"
+
+
+def test_phase_timer_cpu():
+    import time
+    from mpi_cuda_b200.utils.timing import PhaseTimer, write_chrome_trace
+    t = PhaseTimer()
+    with t.phase("a"):
+        time.sleep(0.01)
+    with t.phase("a"):
+        time.sleep(0.01)
+    with t.phase("b"):
+        pass
+    r = t.result()
+    assert r["a"] >= 0.02 and r["b"] >= 0.0 and set(r) == {"a", "b"}
