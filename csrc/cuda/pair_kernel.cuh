@@ -70,6 +70,7 @@ struct alignas(64) PairParams {
   double a1, b1, c1x, c1y, c1z, ct1;   // level n+1 coefficients / time factor
   double a2, b2, c2x, c2y, c2z, ct2;   // level n+2
   const double* ct_ptr;                // if non-null: ct1 = ct_ptr[0], ct2 = ct_ptr[1] (host-fed device table)
+  int skip_b;                          // b1 == 0: u^{n-1} is not read at all (its smem boxes are zero-filled once)
   ErrCtl err1, err2;
   TileGeom tile;
   const int* order;
@@ -102,7 +103,8 @@ __device__ __forceinline__ void pair_issue(const PairParams& P, uint64_t* full, 
                                            int y0, int z0, int nzc) {
   const int s = t % Cfg::kStages;
   const int p = z0 - 2 + t;
-  const bool need_b = (t >= 1 && t <= nzc + 2);       // planes z0-1 .. z1
+  // planes z0-1 .. z1 of u^{n-1}; none at all when its coefficient is zero (Taylor first step)
+  const bool need_b = (t >= 1 && t <= nzc + 2) && !P.skip_b;
   uint8_t* st = stage0 + (size_t)s * Cfg::kStageBytes;
   mbar_arrive_expect_tx(full + s, (uint32_t)(Cfg::kATx + (need_b ? Cfg::kBTx : 0)));
   tma_load_3d(st, &P.map_a, full + s, P.g.xoff + x0 - 2, y0 - 2, p);
@@ -316,6 +318,14 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
     tma_prefetch_desc(&P.map_b);
     if (mask) wait_peer_flags(P, mask);      // ghosts of u^n must have arrived before they are loaded
     for (int t = 0; t < STAGES && t < iters; ++t) pair_issue<Cfg>(P, full, stage0, t, x0, y0, z0, nzc);
+  }
+  if (P.skip_b) {
+    // the previous level has coefficient 0 in this pass: instead of streaming it (8 B per node),
+    // the consumers read zeros — fma(0, 0, acc) is exactly what a zero-initialised array gives
+    for (int s = 0; s < STAGES; ++s) {
+      double* bs = reinterpret_cast<double*>(stage0 + (size_t)s * Cfg::kStageBytes + Cfg::kABytes);
+      for (int i = threadIdx.x; i < Cfg::kBBytes / 8; i += Cfg::kThreads) bs[i] = 0.0;
+    }
   }
   // z slice of the analytic table for the error epilogue (a global load per plane inside the
   // loop exposed its full latency to every warp: ncu, top long-scoreboard stall)

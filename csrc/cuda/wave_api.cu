@@ -605,6 +605,7 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
   P.a2 = a2; P.b2 = b2; P.c2x = cscale2 * p->d.coef[0]; P.c2y = cscale2 * p->d.coef[1]; P.c2z = cscale2 * p->d.coef[2];
   P.ct1 = ct1; P.ct2 = ct2;
   P.ct_ptr = p->ct_table ? p->ct_table + (s + 1) : nullptr;
+  P.skip_b = (b1 == 0.0) ? 1 : 0;
   P.err1 = err_ctl(p, 0, err1);
   P.err2 = err_ctl(p, 1, err2);
   set_bcast(p, &P.err1, err1);
