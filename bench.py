@@ -245,23 +245,13 @@ def main() -> int:
         omx, ol2 = oracle_errors(p, n)
         valid = bool(abs(mx - omx) <= 1e-13 + 1e-5 * omx and abs(l2 - ol2) <= 1e-13 + 1e-5 * ol2)
     pub = PUBLISHED_GLUPS.get(world, PUBLISHED_GLUPS[2])
-    peaks = {}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
-            peaks = json.load(fh)
-    except Exception:
-        pass
-    hbm = peaks.get("hbm_gbs", 6650.0)
     from mpi_cuda_b200.parallel.decomp import plan_all
-    blocks = plan_all(p, dims)
-    # minimum HBM traffic per node and step: 24 B for one pass per step (read u^n, read u^{n-1},
-    # write u^{n+1}); 16 B when two steps share a pass (read 2 levels, write 2 levels per 2 steps)
+    from mpi_cuda_b200.utils import roofline
+    hbm, peaks = roofline.measured_peaks(ROOT)
     pair_mode = bool(args.pair) and args.backend == "fused"
-    bytes_per_node = 16 if pair_mode else 24
-    nodes_per_gpu = max((b.n[0] + 2) * (b.n[1] + 2) * (b.n[2] + 2) for b in blocks)
-    bytes_per_gpu = nodes_per_gpu * bytes_per_node
-    halo_bytes = max(b.halo_bytes_per_step() for b in blocks)
-    t_roof_ms = max(bytes_per_gpu / (hbm * 1e9), halo_bytes / 770e9) * 1e3
+    rf = roofline.step_roofline(plan_all(p, dims), pair_mode, hbm)
+    bytes_per_node, nodes_per_gpu = rf["bytes_per_node_per_step"], rf["nodes_per_gpu"]
+    bytes_per_gpu, halo_bytes, t_roof_ms = rf["bytes_per_gpu_per_step"], rf["halo_bytes_per_gpu_per_step"], rf["roofline_ms_per_step"]
     out = {
         "metric": "GLUP/s at %s grid, K=%d steps, fp64, device-timed max over ranks (wall_s = total)" % (grid_name, K),
         "value": glups, "unit": "GLUP/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -280,7 +270,7 @@ def main() -> int:
                      "halo_bytes_per_gpu_per_step": halo_bytes, "roofline_ms_per_step": t_roof_ms,
                      "fraction_of_roofline": t_roof_ms / (t_ms / K), "of": "measured" if peaks else "fallback",
                      "bytes_per_node_per_step": bytes_per_node,
-                     "vs_single_pass_roofline": (nodes_per_gpu * 24 / (hbm * 1e9) * 1e3) / (t_ms / K)},
+                     "vs_single_pass_roofline": rf["single_pass_roofline_ms_per_step"] / (t_ms / K)},
         "clocks": clocks, "gpu_launches": launches, "validated_vs_oracle": valid,
         "last_error_line": trace[-1] if trace else None,
     }

@@ -144,3 +144,17 @@ def test_phase_timer_cpu():
         pass
     r = t.result()
     assert r["a"] >= 0.02 and r["b"] >= 0.0 and set(r) == {"a", "b"}
+
+
+def test_roofline_arithmetic():
+    from mpi_cuda_b200.parallel.decomp import plan_all
+    from mpi_cuda_b200.utils import roofline
+    p = WaveProblem(512, 1.0, 1e-3, 20)
+    one = roofline.step_roofline(plan_all(p, (1, 1, 1)), False, 6539.9)
+    assert one["nodes_per_gpu"] == 513 ** 3 and one["halo_bytes_per_gpu_per_step"] == 0
+    assert abs(one["roofline_ms_per_step"] - 0.4954) < 1e-3          # 0.495 ms
+    two = roofline.step_roofline(plan_all(p, (1, 1, 1)), True, 6539.9)
+    assert abs(two["roofline_ms_per_step"] * 3 - one["roofline_ms_per_step"] * 2) < 1e-9
+    slab = roofline.step_roofline(plan_all(p, (1, 1, 8)), True, 6539.9)
+    assert slab["halo_bytes_per_gpu_per_step"] == 2 * 511 * 511 * 8
+    assert slab["roofline_ms_per_step"] < one["roofline_ms_per_step"] / 8 * 1.1
