@@ -561,7 +561,8 @@ __global__ void __launch_bounds__(1024, 1) fixup_kernel(const __grid_constant__ 
 }
 
 // K1: analytic layer 0 on every node (ghosts and row padding included) of `u`, zeros in
-// `z` (the array that will receive level 1): one warp per row, coalesced stores.
+// `z` (the array that will receive level 1; may be null when nobody reads it before it is
+// overwritten): one warp per row, coalesced stores.
 __global__ void __launch_bounds__(256) init_kernel(double* __restrict__ u, double* __restrict__ z, Geometry g,
                                                    const double* __restrict__ sx, const double* __restrict__ sy,
                                                    const double* __restrict__ sz) {
@@ -582,7 +583,7 @@ __global__ void __launch_bounds__(256) init_kernel(double* __restrict__ u, doubl
       double v = 0.0;
       if (i >= 0 && i <= g.n[0] + 1) v = sx[i] * syz;
       ur[xe] = v;
-      zr[xe] = 0.0;
+      if (z != nullptr) zr[xe] = 0.0;
     }
   }
 }

@@ -387,12 +387,15 @@ int w3d_plan_set_ct_table(W3dPlan* plan, const double* dev_table) {
 const char* w3d_plan_describe(W3dPlan* plan) { return plan ? plan->text : ""; }
 long long w3d_plan_launches(W3dPlan* plan) { return plan ? plan->launches : 0; }
 
-int w3d_plan_init(W3dPlan* p, void* stream) {
+int w3d_plan_init(W3dPlan* p, void* stream) { return w3d_plan_init_ex(p, stream, 1); }
+
+int w3d_plan_init_ex(W3dPlan* p, void* stream, int zero_second) {
   if (!p) return fail(W3D_EINVAL, "null plan");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long rows = (long long)(p->g.n[2] + 2) * (p->g.n[1] + 2);
   const int blocks = (int)std::max<long long>(1, std::min<long long>((rows + 7) / 8, (long long)p->num_sms * 32));
-  init_kernel<<<blocks, 256, 0, st>>>(p->d.field[0], p->d.field[1], p->g, p->d.tab[0], p->d.tab[1], p->d.tab[2]);
+  init_kernel<<<blocks, 256, 0, st>>>(p->d.field[0], zero_second ? p->d.field[1] : nullptr, p->g, p->d.tab[0],
+                                      p->d.tab[1], p->d.tab[2]);
   CUDA_TRY(cudaGetLastError());
   ++p->launches;
   CUDA_TRY(cudaMemsetAsync(p->d.flags_in, 0, 6 * sizeof(unsigned long long), st));

@@ -95,6 +95,10 @@ int w3d_plan_set_ct_table(W3dPlan* plan, const double* dev_table);
 /* field[0] <- analytic u0 on every node incl. ghosts, field[1] <- 0; clears flags,
  * status and workspace counters (K1; report.pdf p.5 §2.2 item 1). */
 int w3d_plan_init(W3dPlan* plan, void* stream);
+/* zero_second = 0 leaves field[1] untouched: valid when the first thing that happens to it is
+ * being overwritten — a pair-mode run with an even number of steps (its first pass does not read
+ * the previous level at all, the second pass writes field[0..1]).  Saves 8 B per node of init. */
+int w3d_plan_init_ex(W3dPlan* plan, void* stream, int zero_second);
 
 /* One time step producing level s+1 from levels s (cur = field[s&1]) and s-1
  * (stored in field[(s+1)&1], overwritten in place):

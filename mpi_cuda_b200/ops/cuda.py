@@ -62,6 +62,7 @@ def lib() -> C.CDLL:
     l.w3d_plan_launches.argtypes = [vp]
     l.w3d_plan_launches.restype = C.c_longlong
     l.w3d_plan_init.argtypes = [vp, vp]
+    l.w3d_plan_init_ex.argtypes = [vp, vp, C.c_int]
     l.w3d_plan_set_ct_table.argtypes = [vp, vp]
     l.w3d_step_fused.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
     l.w3d_step_tma.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, i32p, i32p, vp, C.c_int, vp]
@@ -185,8 +186,8 @@ class CudaPlan:
     def launches(self) -> int:
         return int(lib().w3d_plan_launches(self._h))
 
-    def init(self) -> None:
-        check(lib().w3d_plan_init(self._h, stream_ptr()))
+    def init(self, zero_second: bool = True) -> None:
+        check(lib().w3d_plan_init_ex(self._h, stream_ptr(), int(zero_second)))
 
     def set_ct_table(self, table: Optional[torch.Tensor]) -> None:
         self._ct_table = table

@@ -52,6 +52,8 @@ class FusedSolver:
                  group=None, every: int = 2, variant: int = -1, zchunk: int = 0, use_graph: bool = True,
                  spin_timeout_ms: int = 0, pair: bool = False, pair_variant: int = -1):
         self._launches_per_run = p.K
+        # pair mode with an even K never reads array 1 before overwriting it
+        self._zero_second = not (pair and p.K % 2 == 0)
         self.p, self.dims, self.every = p, tuple(int(d) for d in dims), every
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -144,13 +146,17 @@ class FusedSolver:
 
         All ranks must have finished this before any rank's first step may push
         into their ghosts, hence the barrier."""
-        self.plan.init()
+        self.plan.init(zero_second=self._zero_second)
         self.table[self.rank].zero_()                    # only my own row: peers clear theirs
         self.barrier()
 
     def step(self, n: int, want_err: bool = True) -> None:
         """Produce time level n (n = 1 is the Taylor step)."""
         a, b, cs = step_coeffs(n)
+        if n == 1 and not self._zero_second:
+            # init() skipped the zero fill of array 1 (even-K pair runs never read it); this
+            # single Taylor step does read it (times b = 0), so make sure it holds finite zeros
+            self.f[1].zero_()
         self.plan.step_fused(n - 1, a, b, cs, float(self.ct[n]), self.trace[n] if want_err else None)
         self.kernel_launches += 1
 
@@ -256,7 +262,7 @@ class FusedSolver:
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
         self.barrier()
         ev[0].record()
-        self.plan.init()
+        self.plan.init(zero_second=self._zero_second)
         self.table[self.rank].zero_()
         self.barrier()          # flags must be reset everywhere before anyone pushes
         ev[1].record()
