@@ -74,5 +74,9 @@ for path, name in (("pair", "2048_pair_block"), ("single", "2048_fused_block")):
                    f"{d['value']:.1f} GLUP/s, {d['roofline']['fraction_of_roofline']:.3f} of its roofline, SM clock "
                    f"{d['clocks']['sm_mhz']} MHz under {d['clocks']['reasons']}; step-1000 error line {d['last_error_line']} "
                    "matches the oracle.")
+EXTRA = os.path.join(ROOT, "profiles", "scaling_extra.md")      # hand-written sections appended verbatim
+if os.path.exists(EXTRA):
+    out.append("")
+    out.append(open(EXTRA).read().rstrip())
 open(os.path.join(ROOT, "profiles", "scaling.md"), "w").write("\n".join(out) + "\n")
 print("\n".join(out))
