@@ -77,7 +77,8 @@ def _gloo_work(rank, world, dims, bc, N, K):
     return res.trace, res.phases
 
 
-@pytest.mark.parametrize("world,dims,bc", [(2, (1, 1, 2), "ddd"), (4, (1, 2, 2), "ddp"), (2, (1, 1, 2), "ddp")])
+@pytest.mark.parametrize("world,dims,bc", [(2, (1, 1, 2), "ddd"), (4, (1, 2, 2), "ddp"), (2, (1, 1, 2), "ddp"),
+                                           (8, (2, 2, 2), "dpd")])
 def test_gloo_rank_count_invariance(world, dims, bc):
     N, K = 28, 6
     base, _ = cpu.solve(WaveProblem(N, 1.0, 1e-3, K, bc=bc), every=2)
