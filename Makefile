@@ -33,7 +33,10 @@ $(OUT)/libwave3d_b200.so: $(CU_SRCS) $(CU_HDRS)
 	@mkdir -p $(OUT)
 	$(NVCC) $(NVCCFLAGS) -shared -o $@ $(CU_SRCS) -cudart static
 
-tools: $(BIN)/mpigpu $(BIN)/tma_probe3
+tools: $(BIN)/mpigpu
+
+# not part of `make all`: `make probe`
+probe: $(BIN)/tma_probe3
 
 # bring-up probe that established the 16-byte TMA coordinate rule
 $(BIN)/tma_probe3: csrc/tools/tma_probe3.cu csrc/cuda/ptx.cuh
@@ -51,4 +54,4 @@ sass: $(OUT)/libwave3d_b200.so
 clean:
 	rm -rf $(OUT)/*.so $(BIN) build
 
-.PHONY: all cpu cuda tools sass clean
+.PHONY: all cpu cuda tools probe sass clean

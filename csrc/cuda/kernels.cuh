@@ -95,7 +95,9 @@ struct alignas(64) StepParams {
   const unsigned long long* flags_in;
   unsigned* shell_counter;
   unsigned* status;
-  int debug_skip;                  // diagnostics only (W3D_DEBUG_SKIP): 1 no flag wait, 2 no copy-out, 4 no fence/release
+#ifdef W3D_DIAG
+  int debug_skip;                  // diagnostic builds only (W3D_DEBUG_SKIP): 1 no flag wait, 2 no copy-out, 4 no fence/release
+#endif
   unsigned long long level;        // level of `cur`
   unsigned long long timeout_ns;
 };
@@ -256,7 +258,17 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+#ifdef W3D_DIAG
+#define W3D_DIAG_SKIP(P, bit) ((P).debug_skip & (bit))
+#else
+#define W3D_DIAG_SKIP(P, bit) 0
+#endif
+
 // Spin (bounded) until the neighbours named in `mask` have delivered level P.level.
+// The ghost layers were written by the peer through the generic proxy (st.global) and are
+// about to be read by TMA (async proxy): the acquire alone does not order those two, so the
+// wait ends with a cross-proxy fence (PTX memory model, "proxy fence"; one instruction per
+// waiting CTA).
 template <class PT>
 __device__ __noinline__ void wait_peer_flags(const PT& P, int mask) {
   for (int f = 0; f < 6; ++f) {
@@ -270,6 +282,7 @@ __device__ __noinline__ void wait_peer_flags(const PT& P, int mask) {
       }
     }
   }
+  fence_proxy_async_global();
 }
 
 // Called by ONE thread of a face CTA after all of the CTA's stores are ordered before
@@ -311,17 +324,21 @@ struct TileCfg {
   static_assert(2 * STAGES * 8 <= 128, "barrier area");
 };
 
-// faces of the block that the tile (tx,ty,ch) touches and that have a neighbour: bit axis*2+side
+// Faces with a neighbour that the tile [lo,hi) comes within `reach` layers of: bit axis*2+side.
+// reach 1: the tile owns nodes of the edge layer (1 or n) — it reads the ghost layer and is the
+// one that copies the edge layer out.  reach 2 (two steps per pass): the tile's level-1 ring
+// reaches the edge layer, so it reads the ghost layer although it may own no edge node.
+// The host mirrors this in face_mask_host() (wave_api.cu).
 template <class PT>
 __device__ __forceinline__ int tile_face_mask(const PT& P, int x0, int y0, int z0, int z1, int tx_w,
-                                              int ty_w) {
+                                              int ty_w, int reach = 1) {
   if (!P.use_flags) return 0;
   int m = 0;
   const int lo[3] = {x0, y0, z0}, hi[3] = {x0 + tx_w, y0 + ty_w, z1};
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
-    if (P.peer[d * 2].active && lo[d] <= 1 && hi[d] > 1) m |= 1 << (d * 2);
-    if (P.peer[d * 2 + 1].active && lo[d] <= P.g.n[d] && hi[d] > P.g.n[d]) m |= 1 << (d * 2 + 1);
+    if (P.peer[d * 2].active && lo[d] <= reach && hi[d] > 1) m |= 1 << (d * 2);
+    if (P.peer[d * 2 + 1].active && lo[d] <= P.g.n[d] && hi[d] > P.g.n[d] - reach + 1) m |= 1 << (d * 2 + 1);
   }
   return m;
 }
@@ -406,7 +423,7 @@ __device__ __forceinline__ void tma_role(const StepParams& P, int x0, int y0, in
       tma_prefetch_desc(&P.map_halo);
       tma_prefetch_desc(&P.map_core);
       // ghosts of the current level must have arrived before they are loaded
-      if (mask && !(P.debug_skip & 1)) wait_peer_flags(P, mask);
+      if (mask && !W3D_DIAG_SKIP(P, 1)) wait_peer_flags(P, mask);
     }
     for (int t = 0; t < iters; ++t) {
       if (leader) {
@@ -490,9 +507,9 @@ __device__ __forceinline__ void tma_role(const StepParams& P, int x0, int y0, in
   }
   if (mask) {
     named_bar_sync(kConsBarrier, Cfg::kConsumers);   // the tile is written (CTA-visible)
-    if (!(P.debug_skip & 2)) face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kConsumers);
+    if (!W3D_DIAG_SKIP(P, 2)) face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kConsumers);
     named_bar_sync(kConsBarrier, Cfg::kConsumers);   // every consumer's peer stores are issued
-    if (threadIdx.x == 0 && !(P.debug_skip & 4)) face_cta_done(P);
+    if (threadIdx.x == 0 && !W3D_DIAG_SKIP(P, 4)) face_cta_done(P);
   }
 }
 

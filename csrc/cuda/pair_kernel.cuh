@@ -81,7 +81,6 @@ struct alignas(64) PairParams {
   double* nxt;
   int n_face_ctas;
   int use_flags;
-  int debug_skip;
   PeerDev peer[6];
   const unsigned long long* flags_in;
   unsigned* shell_counter;
@@ -310,13 +309,17 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
   const int iters = nzc + 4;          // planes z0-2 .. z1+1 of u^n
 
   double mx1 = 0.0, s21 = 0.0, mx2 = 0.0, s22 = 0.0;
-  const int mask = tile_face_mask(P, x0, y0, z0, z1, TX, Cfg::kTY);
+  // copy-out mask: faces whose edge layer this tile owns; wait mask: faces whose ghost layer it
+  // reads — the level-1 ring reaches one node further than the tile, so a tile that ends one
+  // layer short of a face (hi == n, lo == 2) reads that ghost too and has to wait for it
+  const int mask = tile_face_mask(P, x0, y0, z0, z1, TX, Cfg::kTY, 1);
+  const int wmask = tile_face_mask(P, x0, y0, z0, z1, TX, Cfg::kTY, 2);
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
     fence_barrier_init();
     tma_prefetch_desc(&P.map_a);
     tma_prefetch_desc(&P.map_b);
-    if (mask) wait_peer_flags(P, mask);      // ghosts of u^n must have arrived before they are loaded
+    if (wmask) wait_peer_flags(P, wmask);    // ghosts of u^n must have arrived before they are loaded
     for (int t = 0; t < STAGES && t < iters; ++t) pair_issue<Cfg>(P, full, stage0, t, x0, y0, z0, nzc);
   }
   if (P.skip_b) {

@@ -207,6 +207,16 @@ void plan_tiles(const W3dPlan* p, const int lo[3], const int hi[3], int zchunk, 
   t->nchunks = (ez + t->zc - 1) / t->zc;
 }
 
+// host mirror of tile_face_mask() (kernels.cuh)
+int face_mask_host(const W3dPlanDesc& d, const int n[3], const int lo[3], const int hi[3], int reach) {
+  int m = 0;
+  for (int a = 0; a < 3; ++a) {
+    if (d.peer[a * 2].active && lo[a] <= reach && hi[a] > 1) m |= 1 << (a * 2);
+    if (d.peer[a * 2 + 1].active && lo[a] <= n[a] && hi[a] > n[a] - reach + 1) m |= 1 << (a * 2 + 1);
+  }
+  return m;
+}
+
 void add_box(BoxTable* B, const int lo[3], const int hi[3]) {
   for (int d = 0; d < 3; ++d)
     if (hi[d] <= lo[d]) return;
@@ -336,27 +346,12 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
       const int tx = w % t.ntx, ty = (w / t.ntx) % t.nty, ch = w / (t.ntx * t.nty);
       const int lo[3] = {t.x0 + tx * v.tx, t.lo[1] + ty * v.ty, t.lo[2] + ch * t.zc};
       const int hi[3] = {lo[0] + v.tx, lo[1] + v.ty, std::min(lo[2] + t.zc, t.hi[2])};
-      bool is_face = false;
-      for (int d = 0; d < 3; ++d) {
-        if (desc->peer[d * 2].active && lo[d] <= 1 && hi[d] > 1) is_face = true;
-        if (desc->peer[d * 2 + 1].active && lo[d] <= b.n[d] && hi[d] > b.n[d]) is_face = true;
-      }
-      (is_face ? face : rest).push_back(w);
+      (face_mask_host(*desc, p->g.n, lo, hi, 1) ? face : rest).push_back(w);
     }
     p->n_face_ctas = (int)face.size();
-    // Even steps sweep the block upwards, odd steps downwards: the planes written last by
-    // step s are the first ones read by step s+1, so whatever the 126 MB L2 still holds of
-    // them is not fetched from HBM again (matters when the local block is a few L2 sizes).
-    std::vector<int> fwd(face), bwd(face.rbegin(), face.rend());
+    std::vector<int> fwd(face);
     fwd.insert(fwd.end(), rest.begin(), rest.end());
-    // (measured: no gain on B200 at 512^3 .. 512x256x128 — profiles/halo_designs.md — so it is
-    // opt-in via W3D_SWEEP_REVERSAL=1 and the default is the same order on every step)
-    const char* rev = std::getenv("W3D_SWEEP_REVERSAL");
-    if (rev && rev[0] == '1') bwd.insert(bwd.end(), rest.rbegin(), rest.rend());
-    else bwd = fwd;
     cudaError_t ce = cudaMemcpy(p->order_dev, fwd.data(), fwd.size() * sizeof(int), cudaMemcpyHostToDevice);
-    if (ce == cudaSuccess)
-      ce = cudaMemcpy(p->order_dev + W3D_MAX_PARTIALS, bwd.data(), bwd.size() * sizeof(int), cudaMemcpyHostToDevice);
     if (ce != cudaSuccess) {
       delete p;
       return fail(W3D_ECUDA, "cudaMemcpy(order table): %s", cudaGetErrorString(ce));
@@ -429,7 +424,9 @@ int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double 
     P.peer[f].plane = q.plane;
     P.peer[f].flag = q.flag;
   }
+#ifdef W3D_DIAG
   if (const char* dbg = std::getenv("W3D_DEBUG_SKIP")) P.debug_skip = std::atoi(dbg);   // timing diagnostics, wrong results
+#endif
   P.flags_in = p->d.flags_in;
   P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
   return launch_fused(p, P, p->n_ctas, static_cast<cudaStream_t>(stream));
@@ -551,19 +548,19 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const*
       return fail(W3D_EINVAL, "face %d has a neighbour but no peer aux arrays were given", f);
   }
   {
-    std::vector<int> face, rest;
+    // order: tiles that own an edge layer (they wait, copy out and are counted for the release),
+    // then tiles that only read a ghost layer through their level-1 ring (they wait), then the rest
+    std::vector<int> face, waiters, rest;
     for (int w = 0; w < p->pn_ctas; ++w) {
       const int tx = w % t.ntx, ty = (w / t.ntx) % t.nty, ch = w / (t.ntx * t.nty);
       const int lo[3] = {t.x0 + tx * v.tx, t.lo[1] + ty * v.ty, t.lo[2] + ch * t.zc};
       const int hi[3] = {lo[0] + v.tx, lo[1] + v.ty, std::min(lo[2] + t.zc, t.hi[2])};
-      bool is_face = false;
-      for (int d = 0; d < 3; ++d) {
-        if (p->d.peer[d * 2].active && lo[d] <= 1 && hi[d] > 1) is_face = true;
-        if (p->d.peer[d * 2 + 1].active && lo[d] <= p->g.n[d] && hi[d] > p->g.n[d]) is_face = true;
-      }
-      (is_face ? face : rest).push_back(w);
+      if (face_mask_host(p->d, p->g.n, lo, hi, 1)) face.push_back(w);
+      else if (face_mask_host(p->d, p->g.n, lo, hi, 2)) waiters.push_back(w);
+      else rest.push_back(w);
     }
     p->pn_face_ctas = (int)face.size();
+    face.insert(face.end(), waiters.begin(), waiters.end());
     face.insert(face.end(), rest.begin(), rest.end());
     CUDA_TRY(cudaMemcpy(p->order_dev + W3D_MAX_PARTIALS, face.data(), face.size() * sizeof(int),
                         cudaMemcpyHostToDevice));
