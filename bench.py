@@ -194,6 +194,12 @@ def main() -> int:
         s.check_status()
         trace = s.gather_trace()
         extra["plan"] = s.describe()
+        # exchange measured inside the kernels during the LAST timed repetition (counters are reset by init):
+        # per launch the longest flag wait / halo copy-out over the face CTAs, summed over the launches
+        xs = s.exchange_stats()
+        extra["exchange"] = {"flag_wait_ms_per_step": xs["flag_wait_s"] * 1e3 / K, "halo_copy_ms_per_step": xs["halo_copy_s"] * 1e3 / K,
+                             "max_flag_wait_us": xs["max_flag_wait_s"] * 1e6, "max_halo_copy_us": xs["max_halo_copy_s"] * 1e6,
+                             "handshakes": xs["launches"], "measured": "%globaltimer stamps in the face CTAs, max over CTAs and ranks"}
         # ---- end to end through the public step API: per step H2D of the step's
         #      input (time factor, pinned host) and D2H of the step's result ----
         e2e = None

@@ -36,6 +36,15 @@ struct Geometry {
   int n[3];
   int xoff;
   long long pitch, plane;
+  int gs;   // ghost depth - 1: rows / planes that exist in front of local index 0 (TMA maps of the
+            // two-steps-per-pass kernel are encoded over the whole allocation and shift y, z by gs)
+};
+
+// Device-side exchange statistics (u64 words in the workspace, see W3D_XSTAT_* in wave3d.h):
+// every face CTA reports how long it spun on the neighbours' flags and how long its halo
+// copy-out took; the last face CTA of a launch folds the per-launch maxima into running totals.
+struct XStat {
+  unsigned long long cur_wait, cur_copy, sum_wait, sum_copy, launches, max_wait, max_copy, pad;
 };
 
 struct PeerDev {
@@ -95,6 +104,9 @@ struct alignas(64) StepParams {
   const unsigned long long* flags_in;
   unsigned* shell_counter;
   unsigned* status;
+  XStat* xstat;
+  unsigned long long release;      // level published to the neighbours when the last face CTA is done
+  int halo_depth;                  // layers per face copied out (1; 2 for the wide-halo pair kernel)
 #ifdef W3D_DIAG
   int debug_skip;                  // diagnostic builds only (W3D_DEBUG_SKIP): 1 no flag wait, 2 no copy-out, 4 no fence/release
 #endif
@@ -269,8 +281,10 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 // about to be read by TMA (async proxy): the acquire alone does not order those two, so the
 // wait ends with a cross-proxy fence (PTX memory model, "proxy fence"; one instruction per
 // waiting CTA).
+// Returns the nanoseconds spent here (%globaltimer).
 template <class PT>
-__device__ __noinline__ void wait_peer_flags(const PT& P, int mask) {
+__device__ __noinline__ unsigned long long wait_peer_flags(const PT& P, int mask) {
+  const unsigned long long t_in = globaltimer_ns();
   for (int f = 0; f < 6; ++f) {
     if (!(mask & (1 << f))) continue;
     const unsigned long long t0 = globaltimer_ns();
@@ -283,19 +297,37 @@ __device__ __noinline__ void wait_peer_flags(const PT& P, int mask) {
     }
   }
   fence_proxy_async_global();
+  return globaltimer_ns() - t_in;
 }
 
 // Called by ONE thread of a face CTA after all of the CTA's stores are ordered before
-// it (CTA-scope barrier).  The last face CTA publishes level+1 to every neighbour.
+// it (CTA-scope barrier).  The last face CTA publishes P.release to every neighbour.
+// wait_ns / t_copy0: this CTA's flag-wait time and the %globaltimer stamp taken before its
+// copy-out (exchange statistics, only touched when P.xstat is set).
 template <class PT>
-__device__ __noinline__ void face_cta_done(const PT& P) {
+__device__ __noinline__ void face_cta_done(const PT& P, unsigned long long wait_ns = 0ull,
+                                           unsigned long long t_copy0 = 0ull) {
   __threadfence_system();
+  if (P.xstat) {
+    atomicMax(&P.xstat->cur_wait, wait_ns);
+    atomicMax(&P.xstat->cur_copy, globaltimer_ns() - t_copy0);
+    __threadfence();
+  }
   const unsigned done = atomicAdd(P.shell_counter, 1u);
   if (done == (unsigned)P.n_face_ctas - 1u) {
     *P.shell_counter = 0u;
     __threadfence_system();
     for (int f = 0; f < 6; ++f)
-      if (P.peer[f].active) st_release_sys(P.peer[f].flag, P.level + 1ull);
+      if (P.peer[f].active) st_release_sys(P.peer[f].flag, P.release);
+    if (P.xstat) {
+      XStat* x = P.xstat;
+      const unsigned long long w = atomicExch(&x->cur_wait, 0ull), c = atomicExch(&x->cur_copy, 0ull);
+      x->sum_wait += w;
+      x->sum_copy += c;
+      x->launches += 1ull;
+      if (w > x->max_wait) x->max_wait = w;
+      if (c > x->max_copy) x->max_copy = c;
+    }
   }
 }
 
@@ -347,6 +379,8 @@ __device__ __forceinline__ int tile_face_mask(const PT& P, int x0, int y0, int z
 // layers out of the local array (just written: L2 hits) into the neighbours' ghost
 // layers.  Keeping this out of the streaming loop leaves that loop identical for face
 // and interior CTAs.  tid/nthreads: consumer thread index and count.
+// P.halo_depth layers per face: layer 1+m / n-m of mine fills the neighbour's ghost layer
+// ghost_index+m / ghost_index-m (m = 0 .. depth-1); a tile copies the layers it owns.
 template <class PT>
 __device__ __noinline__ void face_copy_out(const PT& P, int mask, int x0, int y0, int z0, int z1, int tx_w, int ty_w,
                               int tid, int nthreads) {
@@ -357,12 +391,16 @@ __device__ __noinline__ void face_copy_out(const PT& P, int mask, int x0, int y0
   const int yl = max(y0, T.lo[1]), yh = min(y0 + ty_w, T.hi[1]);
   const int ex = xh - xl, ey = yh - yl, ez = z1 - z0;
   if (ex <= 0 || ey <= 0 || ez <= 0) return;
+  const int tlo[3] = {xl, yl, z0}, thi[3] = {xh, yh, z1};
 #pragma unroll 1
-  for (int f = 0; f < 6; ++f) {
+  for (int fm = 0; fm < 6 * P.halo_depth; ++fm) {
+    const int f = fm % 6, m = fm / 6;
     if (!(mask & (1 << f))) continue;
     const PeerDev& pr = P.peer[f];
     const int d = f >> 1;
-    const int layer = (f & 1) ? g.n[d] : 1;          // my edge layer along axis d
+    const int layer = (f & 1) ? g.n[d] - m : 1 + m;   // my m-th layer from that face along axis d
+    if (layer < tlo[d] || layer >= thi[d]) continue;  // another tile owns it
+    const int ghost = pr.ghost_index + ((f & 1) ? -m : m);
     // iterate the two other axes, fastest first
     const int e0 = d == 0 ? ey : ex;                    // fast extent
     const int e1 = d == 2 ? ey : ez;                    // slow extent
@@ -380,7 +418,7 @@ __device__ __noinline__ void face_copy_out(const PT& P, int mask, int x0, int y0
           else if (d == 1) { q[0] = xl + a; q[1] = layer; q[2] = z0 + b; }
           else { q[0] = xl + a; q[1] = yl + b; q[2] = layer; }
           v[u] = __ldcg(P.nxt + gidx(g, q[0], q[1], q[2]));
-          q[d] = pr.ghost_index;
+          q[d] = ghost;
           dst[u] = (long long)q[2] * pr.plane + (long long)q[1] * pr.pitch + g.xoff + q[0];
         }
       }
@@ -423,7 +461,10 @@ __device__ __forceinline__ void tma_role(const StepParams& P, int x0, int y0, in
       tma_prefetch_desc(&P.map_halo);
       tma_prefetch_desc(&P.map_core);
       // ghosts of the current level must have arrived before they are loaded
-      if (mask && !W3D_DIAG_SKIP(P, 1)) wait_peer_flags(P, mask);
+      if (mask && !W3D_DIAG_SKIP(P, 1)) {
+        const unsigned long long w = wait_peer_flags(P, mask);
+        *reinterpret_cast<unsigned long long*>(smem + 128 + 1016) = w;   // handed to consumer thread 0 (read after the CTA barriers below)
+      }
     }
     for (int t = 0; t < iters; ++t) {
       if (leader) {
@@ -507,9 +548,11 @@ __device__ __forceinline__ void tma_role(const StepParams& P, int x0, int y0, in
   }
   if (mask) {
     named_bar_sync(kConsBarrier, Cfg::kConsumers);   // the tile is written (CTA-visible)
+    const unsigned long long t_copy0 = P.xstat ? globaltimer_ns() : 0ull;
     if (!W3D_DIAG_SKIP(P, 2)) face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kConsumers);
     named_bar_sync(kConsBarrier, Cfg::kConsumers);   // every consumer's peer stores are issued
-    if (threadIdx.x == 0 && !W3D_DIAG_SKIP(P, 4)) face_cta_done(P);
+    if (threadIdx.x == 0 && !W3D_DIAG_SKIP(P, 4))
+      face_cta_done(P, *reinterpret_cast<volatile unsigned long long*>(smem + 128 + 1016), t_copy0);
   }
 }
 
@@ -533,7 +576,9 @@ fused_step_kernel(const __grid_constant__ StepParams P) {
   const int y0 = T.lo[1] + ty * Cfg::kTY;
   const int z0 = T.lo[2] + ch * T.zc;
   const int z1 = min(z0 + T.zc, T.hi[2]);
-  const int mask = tile_face_mask(P, x0, y0, z0, z1, Cfg::kTX, Cfg::kTY);
+  // tiles that own one of the halo_depth outermost layers of a face with a neighbour (1 layer; 2 in
+  // plans that keep a wide halo for the two-steps-per-pass kernel): they wait, copy out, are counted
+  const int mask = tile_face_mask(P, x0, y0, z0, z1, Cfg::kTX, Cfg::kTY, P.halo_depth);
   tma_role<Cfg>(P, x0, y0, z0, z1, mask, smem, mx, s2);
   if (P.err.out != nullptr) {
     __syncthreads();
@@ -577,28 +622,31 @@ __global__ void __launch_bounds__(1024, 1) fixup_kernel(const __grid_constant__ 
   publish_error(P.err, mx, s2, red);
 }
 
-// K1: analytic layer 0 on every node (ghosts and row padding included) of `u`, zeros in
-// `z` (the array that will receive level 1; may be null when nobody reads it before it is
-// overwritten): one warp per row, coalesced stores.
+// K1: analytic layer 0 on every node (ghost layers — g.gs + 1 of them — and row padding
+// included) of `u`, zeros in `z` (the array that will receive level 1; may be null when nobody
+// reads it before it is overwritten): one warp per row, coalesced stores.  With two ghost
+// layers the tables are read at indices -1 and n+2 as well.
 __global__ void __launch_bounds__(256) init_kernel(double* __restrict__ u, double* __restrict__ z, Geometry g,
                                                    const double* __restrict__ sx, const double* __restrict__ sy,
                                                    const double* __restrict__ sz) {
-  const int rows_per_plane = g.n[1] + 2;
-  const long long rows = (long long)rows_per_plane * (g.n[2] + 2);
+  const int gs = g.gs;
+  const int rows_per_plane = g.n[1] + 2 + 2 * gs;
+  const long long rows = (long long)rows_per_plane * (g.n[2] + 2 + 2 * gs);
   const int lane = threadIdx.x & 31;
   const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
   const int pitch = (int)g.pitch;
   for (long long row = warp0; row < rows; row += nwarps) {
-    const int j = (int)(row % rows_per_plane);
-    const int k = (int)(row / rows_per_plane);
+    const int j = (int)(row % rows_per_plane) - gs;
+    const int k = (int)(row / rows_per_plane) - gs;
     const double syz = sy[j] * sz[k];
-    double* ur = u + row * g.pitch;
-    double* zr = z + row * g.pitch;
+    const long long off = (long long)k * g.plane + (long long)j * g.pitch;
+    double* ur = u + off;
+    double* zr = z + off;
     for (int xe = lane; xe < pitch; xe += 32) {
       const int i = xe - g.xoff;
       double v = 0.0;
-      if (i >= 0 && i <= g.n[0] + 1) v = sx[i] * syz;
+      if (i >= -gs && i <= g.n[0] + 1 + gs) v = sx[i] * syz;
       ur[xe] = v;
       if (z != nullptr) zr[xe] = 0.0;
     }

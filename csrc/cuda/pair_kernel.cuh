@@ -23,10 +23,19 @@
 //     as the "previous" level), and written to global D;
 //   * both levels can feed the error epilogue.
 // Level-1 values on ring nodes outside the local block are taken as 0 (Dirichlet
-// boundary).  Faces with a neighbour are handled by the host protocol in
-// wave_api.cu (the layer next to such a face is finished by a fix-up launch once the
-// neighbour's level-1 edge has arrived).  The arithmetic is the same
-// w3d_partial/w3d_finish sequence, so results are bit-identical to two single steps.
+// boundary).  Faces with a neighbour (another GPU, or this one across a periodic axis)
+// come in two protocols, chosen by the host (wave_api.cu):
+//   * wide halo (default, one launch and one flag handshake per two steps): the arrays
+//     carry TWO ghost layers.  u^n arrives two layers deep, so level 1 is also formed on
+//     the first ghost layer (redundantly with the neighbour, bit-identical) and kept in
+//     out1's ghost layer as the next pass's u^{n-1} halo; level 2 is then complete on
+//     every owned node and the face CTAs ship its two outermost layers per face.  Same
+//     halo volume per step as one layer per step.
+//   * fix-up (two axes with neighbours: the wide scheme would also need the edge lines of
+//     the diagonal neighbours): one ghost layer; level 2 is left out next to such faces
+//     (skip_lo/hi) and finished by `fixup_kernel` after an exchange of level 1.
+// The arithmetic is the same w3d_partial/w3d_finish sequence, so results are
+// bit-identical to two single steps.
 #pragma once
 #include "kernels.cuh"
 
@@ -78,18 +87,26 @@ struct alignas(64) PairParams {
   // face helpers in kernels.cuh work on both): face CTAs acquire `level` before loading,
   // copy the level-(n+1) face layers of `nxt` (= out1) into the neighbours and the last
   // one releases level+1.
-  double* nxt;
+  double* nxt;            // array whose face layers are shipped: out1 (fix-up protocol) or out2 (wide halo)
   int n_face_ctas;
   int use_flags;
   PeerDev peer[6];
   const unsigned long long* flags_in;
   unsigned* shell_counter;
   unsigned* status;
+  XStat* xstat;
   unsigned long long level;
+  unsigned long long release;
   unsigned long long timeout_ns;
+  int halo_depth;         // 1 (fix-up protocol) or 2 (wide halo)
   // nodes of level 2 that must NOT be produced here: the layer next to a face with a
   // neighbour (their level-1 ghost is not known yet).  skip_lo/hi[d] = 1 when active.
+  // Fix-up protocol only; all zero with the wide halo.
   int skip_lo[3], skip_hi[3];
+  // wide halo: level 1 is meaningful on local indices in_lo[d] .. in_hi[d] (0 / n+1 included
+  // where that face has a neighbour; 1 .. n otherwise), and is stored on the ghost layer too
+  int in_lo[3], in_hi[3];
+  int wide;
 };
 
 // Consumer side of one CTA.  FULL = every node of the tile is inside the block, is
@@ -106,8 +123,9 @@ __device__ __forceinline__ void pair_issue(const PairParams& P, uint64_t* full, 
   const bool need_b = (t >= 1 && t <= nzc + 2) && !P.skip_b;
   uint8_t* st = stage0 + (size_t)s * Cfg::kStageBytes;
   mbar_arrive_expect_tx(full + s, (uint32_t)(Cfg::kATx + (need_b ? Cfg::kBTx : 0)));
-  tma_load_3d(st, &P.map_a, full + s, P.g.xoff + x0 - 2, y0 - 2, p);
-  if (need_b) tma_load_3d(st + Cfg::kABytes, &P.map_b, full + s, P.g.xoff + x0 - 2, y0 - 1, p);
+  const int gs = P.g.gs;   // the maps span the whole allocation: gs ghost rows / planes sit in front of index 0
+  tma_load_3d(st, &P.map_a, full + s, P.g.xoff + x0 - 2, y0 - 2 + gs, p + gs);
+  if (need_b) tma_load_3d(st + Cfg::kABytes, &P.map_b, full + s, P.g.xoff + x0 - 2, y0 - 1 + gs, p + gs);
 }
 
 template <class Cfg, bool FULL, bool XFULL>
@@ -124,24 +142,29 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
   const int cxi = tid % TX;
   const int r0 = (tid / TX) * RPT;
   const int gx = x0 + cxi;
-  const bool x_in = gx >= 1 && gx <= g.n[0];                 // inside the local block
+  const bool x_in = gx >= P.in_lo[0] && gx <= P.in_hi[0];    // level 1 exists here (block, or first ghost layer of a wide halo)
   const bool x_ok = gx >= T.lo[0] && gx < T.hi[0];           // this launch updates it
   const bool want1 = P.err1.out != nullptr, want2 = P.err2.out != nullptr;
   const double ct1 = P.ct_ptr ? __ldg(P.ct_ptr) : P.ct1, ct2 = P.ct_ptr ? __ldg(P.ct_ptr + 1) : P.ct2;
   double acc1[RPT], zA[RPT], acc2[RPT], zL[RPT], sxy[RPT];
   double zA1[RPT], zL1[RPT];            // second register set of the z pipeline (see `iter`)
-  bool in1[RPT], st1[RPT], st2[RPT];
+  bool in1[RPT], st1[RPT], st2[RPT], own[RPT];
   const double sxv = x_in ? P.sx[gx] : 0.0;
 #pragma unroll
   for (int r = 0; r < RPT; ++r) {
     const int gy = y0 + r0 + r;
-    const bool y_in = gy >= 1 && gy <= g.n[1];
+    const bool y_in = gy >= P.in_lo[1] && gy <= P.in_hi[1];
+    const bool y_ok = gy >= T.lo[1] && gy < T.hi[1];
     // FULL: the tile is complete in y and free of skipped rows, so only the thread-constant
     // x conditions remain (a partial last tile in x just switches whole columns off)
     // XFULL additionally: complete in x and free of skipped columns -> no predicate at all
     in1[r] = (XFULL || x_in) && (FULL || y_in);                             // level 1 is meaningful here
-    st1[r] = (XFULL || x_ok) && (FULL || (gy >= T.lo[1] && gy < T.hi[1]));  // level 1 is stored from here
-    st2[r] = st1[r] && (XFULL || (!(P.skip_lo[0] && gx == 1) && !(P.skip_hi[0] && gx == g.n[0]))) &&
+    own[r] = (XFULL || x_ok) && (FULL || y_ok);                             // an owned node this launch updates
+    // level 1 is stored on owned nodes and, with a wide halo, on first-ghost-layer nodes that fall
+    // inside a partial tile (ghost along exactly one of x / y; edges are never needed)
+    const bool xg = gx < 1 || gx > g.n[0], yg = gy < 1 || gy > g.n[1];
+    st1[r] = own[r] || (!(FULL && XFULL) && P.wide && in1[r] && ((xg && y_ok) || (yg && x_ok)));
+    st2[r] = own[r] && (XFULL || (!(P.skip_lo[0] && gx == 1) && !(P.skip_hi[0] && gx == g.n[0]))) &&
              (FULL || (!(P.skip_lo[1] && gy == 1) && !(P.skip_hi[1] && gy == g.n[1])));
     sxy[r] = in1[r] ? sxv * P.sy[min(max(gy, 0), g.n[1] + 1)] : 0.0;
     acc1[r] = zA[r] = acc2[r] = zL[r] = zA1[r] = zL1[r] = 0.0;
@@ -155,9 +178,20 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
     else { const int q = tid - 2 * W1; rcx = (q & 1) ? W1 - 1 : 0; rry = 1 + (q >> 1); }
   }
   const int rgx = x0 - 1 + rcx, rgy = y0 - 1 + rry;
-  const bool ring_in = has_ring && rgx >= 1 && rgx <= g.n[0] && rgy >= 1 && rgy <= g.n[1];
+  const bool ring_in = has_ring && rgx >= P.in_lo[0] && rgx <= P.in_hi[0] && rgy >= P.in_lo[1] && rgy <= P.in_hi[1];
+  // wide halo: a ring node on the first ghost layer of x (or y) whose other coordinate is an
+  // owned row (column) of this tile keeps its level-1 value in out1's ghost layer
+  const bool ring_xg = rgx < 1 || rgx > g.n[0], ring_yg = rgy < 1 || rgy > g.n[1];
+  const bool ring_st = P.wide && ring_in && (ring_xg != ring_yg) &&
+                       (ring_xg ? (rgy >= max(y0, T.lo[1]) && rgy < min(y0 + Cfg::kTY, T.hi[1]))
+                                : (rgx >= max(x0, T.lo[0]) && rgx < min(x0 + TX, T.hi[0])));
+  double* oring = P.out1 + (long long)rgy * g.pitch + g.xoff + rgx;
   double racc = 0.0, rzA = 0.0;
   const int pitch = (int)g.pitch;
+  // z: level 1 exists on planes in_lo[2] .. in_hi[2]; the first ghost plane is stored by the chunk next to it
+  const int zl1_lo = P.in_lo[2], zl1_hi = P.in_hi[2];
+  const int zg_lo = (P.wide && zl1_lo == 0 && z0 == 1) ? 0 : -1000000;
+  const int zg_hi = (P.wide && zl1_hi == g.n[2] + 1 && z1 == g.n[2] + 1) ? g.n[2] + 1 : -1000000;
   double* o1 = P.out1 + (long long)(y0 + r0) * g.pitch + g.xoff + gx;
   double* o2 = P.out2 + (long long)(y0 + r0) * g.pitch + g.xoff + gx;
   // thread-constant shared-memory offsets (elements)
@@ -183,7 +217,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
 #pragma unroll
     for (int r = 0; r < RPT; ++r) zAc[r] = As[offA + (r + 1) * WA];
     const int p1 = p - 1;                                        // level-1 plane completed now
-    const bool p1_live = t >= 2 && p1 >= 1 && p1 <= g.n[2];     // otherwise level 1 is 0 there
+    const bool p1_live = t >= 2 && p1 >= zl1_lo && p1 <= zl1_hi;  // otherwise level 1 is 0 there
     const bool p1_store = p1 >= z0 && p1 < z1;
     const bool p_l1 = p >= z0 - 1 && p <= z1;                   // plane p needs a level-1 partial
 #pragma unroll
@@ -197,6 +231,13 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
     }
 #pragma unroll
     for (int r = 0; r < RPT; ++r) L1w[off1 + r * W1] = zLc[r];
+    if (p1 == zg_lo || p1 == zg_hi) {
+      // wide halo: level 1 on the first ghost plane, kept as the next pass's u^{n-1} halo
+      double* o = o1 + (long long)p1 * g.plane;
+#pragma unroll
+      for (int r = 0; r < RPT; ++r)
+        if (own[r]) o[r * pitch] = zLc[r];
+    }
     if (p1_store) {
       double* o = o1 + (long long)p1 * g.plane;
 #pragma unroll
@@ -206,7 +247,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
         const double szt = s_sz[t - 1] * ct1;      // s_sz[i] = sz[z0 - 2 + i]
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
-          if (st1[r]) {
+          if (own[r]) {
             const double e = w3d_abs_err(zLc[r], sxy[r], szt);
             mx1 = fmax(mx1, e);
             s21 = fma(e, e, s21);
@@ -220,6 +261,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
       double v = w3d_finish(racc, ring_c, P.c1z);
       if (!(ring_in && p1_live)) v = 0.0;
       L1w[offR1] = v;
+      if (ring_st && p1_store) oring[(long long)p1 * g.plane] = v;
     }
     if (p_l1) {
 #pragma unroll
@@ -309,17 +351,19 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
   const int iters = nzc + 4;          // planes z0-2 .. z1+1 of u^n
 
   double mx1 = 0.0, s21 = 0.0, mx2 = 0.0, s22 = 0.0;
-  // copy-out mask: faces whose edge layer this tile owns; wait mask: faces whose ghost layer it
-  // reads — the level-1 ring reaches one node further than the tile, so a tile that ends one
-  // layer short of a face (hi == n, lo == 2) reads that ghost too and has to wait for it
-  const int mask = tile_face_mask(P, x0, y0, z0, z1, TX, Cfg::kTY, 1);
+  // copy-out mask: faces of which this tile owns one of the halo_depth outermost layers; wait
+  // mask: faces whose ghost layers it reads — the level-1 ring reaches one node further than the
+  // tile, so a tile that ends one layer short of a face (hi == n, lo == 2) reads that ghost too
+  // and has to wait for it.  With the wide halo (two layers shipped) the two masks coincide.
+  const int mask = tile_face_mask(P, x0, y0, z0, z1, TX, Cfg::kTY, P.halo_depth);
   const int wmask = tile_face_mask(P, x0, y0, z0, z1, TX, Cfg::kTY, 2);
+  unsigned long long wait_ns = 0ull;
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
     fence_barrier_init();
     tma_prefetch_desc(&P.map_a);
     tma_prefetch_desc(&P.map_b);
-    if (wmask) wait_peer_flags(P, wmask);    // ghosts of u^n must have arrived before they are loaded
+    if (wmask) wait_ns = wait_peer_flags(P, wmask);    // ghosts of u^n must have arrived before they are loaded
     for (int t = 0; t < STAGES && t < iters; ++t) pair_issue<Cfg>(P, full, stage0, t, x0, y0, z0, nzc);
   }
   if (P.skip_b) {
@@ -350,10 +394,11 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
     else
       pair_consumer<Cfg, false, false>(P, full, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
     if (mask) {
-      __syncthreads();   // the tile's level n+1 is written (CTA-visible)
+      __syncthreads();   // the tile's shipped level is written (CTA-visible)
+      const unsigned long long t_copy0 = P.xstat ? globaltimer_ns() : 0ull;
       face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kThreads);
       __syncthreads();
-      if (threadIdx.x == 0) face_cta_done(P);
+      if (threadIdx.x == 0) face_cta_done(P, wait_ns, t_copy0);
     }
   }
   if (P.err1.out != nullptr) {

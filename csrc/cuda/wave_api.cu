@@ -69,6 +69,11 @@ using PCfg4 = PairCfg<64, 4, 8, 3>;
 using PCfg5 = PairCfg<64, 2, 15, 4>;   // 64 x 30 tile, 2 rows per thread: 960 threads (30 warps)
 using PCfg6 = PairCfg<64, 4, 4, 3, 2>; // 64 x 16 tile, 256 threads, ~88 KB: TWO CTAs per SM (small blocks)
 using PCfg7 = PairCfg<64, 4, 4, 4, 2>; // same with a 4-stage ring (~108 KB)
+// 64 x 30 tiles: 511 rows make 18 tiles instead of 16 -> 8 x 18 = 144 CTAs on 148 SMs where
+// 64 x 32 leaves 20 SMs idle (one-wave blocks: 512^3 on 4 and 8 GPUs)
+using PCfg8 = PairCfg<64, 5, 6, 3>;    // 384 threads, 5 rows per thread
+using PCfg9 = PairCfg<64, 3, 10, 3>;   // 640 threads, 3 rows per thread
+using PCfg10 = PairCfg<64, 6, 5, 4>;   // 320 threads, 6 rows per thread, 4-stage ring
 struct PairVariant {
   int tx, ty, threads, smem, ctas_per_sm;
   void (*kernel)(const PairParams);
@@ -83,12 +88,17 @@ const PairVariant kPairVariants[] = {
     {PCfg5::kTX, PCfg5::kTY, PCfg5::kThreads, PCfg5::kSmemBytes, 1, pair_step_kernel<PCfg5>, "pair 64x30x4st rpt2"},
     {PCfg6::kTX, PCfg6::kTY, PCfg6::kThreads, PCfg6::kSmemBytes, 2, pair_step_kernel<PCfg6>, "pair 64x16x3st rpt4 2cta"},
     {PCfg7::kTX, PCfg7::kTY, PCfg7::kThreads, PCfg7::kSmemBytes, 2, pair_step_kernel<PCfg7>, "pair 64x16x4st rpt4 2cta"},
+    {PCfg8::kTX, PCfg8::kTY, PCfg8::kThreads, PCfg8::kSmemBytes, 1, pair_step_kernel<PCfg8>, "pair 64x30x3st rpt5"},
+    {PCfg9::kTX, PCfg9::kTY, PCfg9::kThreads, PCfg9::kSmemBytes, 1, pair_step_kernel<PCfg9>, "pair 64x30x3st rpt3"},
+    {PCfg10::kTX, PCfg10::kTY, PCfg10::kThreads, PCfg10::kSmemBytes, 1, pair_step_kernel<PCfg10>, "pair 64x30x4st rpt6"},
 };
 constexpr int kNumPairVariants = sizeof(kPairVariants) / sizeof(kPairVariants[0]);
 constexpr int kDefaultVariant = 3;   // best of the measured sweep at 512^3 (profiles/variant_sweep.md)
 
 // ---- workspace layout ---------------------------------------------------------------
-constexpr size_t kCounterBytes = 256;   // tickets [0..7] at 0, face-CTA counter at +64
+constexpr size_t kCounterBytes = 256;   // tickets [0..7] at 0, face-CTA counter at +64, exchange statistics (XStat) at +128
+constexpr size_t kXStatOffset = 128;
+static_assert(kXStatOffset + sizeof(XStat) <= kCounterBytes, "workspace header layout");
 constexpr size_t kOrderBytes = 2 * (size_t)W3D_MAX_PARTIALS * sizeof(int);   // block -> tile tables (even / odd steps)
 constexpr size_t kSlotBytes = 2ull * W3D_MAX_PARTIALS * sizeof(double);
 constexpr size_t kSlotBase = kCounterBytes + kOrderBytes;
@@ -117,7 +127,7 @@ struct W3dPlan {
   Geometry g;
   int variant;
   int num_sms;
-  CUtensorMap halo[2], core[2];    // per field array
+  CUtensorMap halo[4], core[4];    // per array (2, 3 = aux arrays once w3d_plan_enable_pairs has run)
   bool maps_ok;
   // fused geometry: the TMA role covers the whole block; CTAs that touch a face
   // with a neighbour come first in `order`
@@ -135,8 +145,10 @@ struct W3dPlan {
   int pn_ctas, pn_face_ctas;
   BoxTable shell;                  // layer next to faces with a neighbour (fix-up pass)
   bool pair_ready;
+  int pair_mode;                   // W3D_PAIR_LOCAL / WIDE / FIXUP
+  int step_depth;                  // halo layers the single-step kernel ships: 1, or 2 in wide-halo plans
   long long launches;
-  char text[768];
+  char text[1024];
 };
 
 namespace {
@@ -152,24 +164,36 @@ ErrCtl err_ctl(const W3dPlan* p, int slot, double* out) {
   return e;
 }
 
-int encode_maps(W3dPlan* p) {
+// One 3-D tiled map over an array.  `ghost` layers of rows / planes in front of local index 0
+// are part of the map (the array pointer is moved back accordingly), so a kernel addresses
+// local (x, y, z) as (xoff + x, y + ghost - 1 ... see Geometry::gs).
+int encode_one(const W3dPlan* p, CUtensorMap* m, double* arr, int box_x, int box_y, int gs, const char* what) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled is not available from the driver");
-  const Variant& v = kVariants[p->variant];
-  const cuuint64_t dims[3] = {(cuuint64_t)p->g.pitch, (cuuint64_t)(p->g.n[1] + 2), (cuuint64_t)(p->g.n[2] + 2)};
+  const cuuint64_t dims[3] = {(cuuint64_t)p->g.pitch, (cuuint64_t)(p->g.n[1] + 2 + 2 * gs),
+                              (cuuint64_t)(p->g.n[2] + 2 + 2 * gs)};
   const cuuint64_t strides[2] = {(cuuint64_t)p->g.pitch * 8, (cuuint64_t)p->g.plane * 8};
   const cuuint32_t estr[3] = {1, 1, 1};
+  const cuuint32_t box[3] = {(cuuint32_t)box_x, (cuuint32_t)box_y, 1};
+  double* base = arr - (long long)gs * (p->g.plane + p->g.pitch);
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled(%s) failed: %d", what, (int)r);
+  return W3D_OK;
+}
+
+// maps of the single-step kernel for array q (one ghost layer is all it addresses)
+int encode_step_maps(W3dPlan* p, int q, double* arr) {
+  const Variant& v = kVariants[p->variant];
+  int rc = encode_one(p, &p->halo[q], arr, v.tx + 4, v.ty + 2, 0, "halo");
+  if (rc == W3D_OK) rc = encode_one(p, &p->core[q], arr, v.tx, v.ty, 0, "core");
+  return rc;
+}
+
+int encode_maps(W3dPlan* p) {
   for (int f = 0; f < 2; ++f) {
-    const cuuint32_t hb[3] = {(cuuint32_t)(v.tx + 4), (cuuint32_t)(v.ty + 2), 1};
-    const cuuint32_t cb[3] = {(cuuint32_t)v.tx, (cuuint32_t)v.ty, 1};
-    CUresult r = enc(&p->halo[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, p->d.field[f], dims, strides, hb, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled(halo) failed: %d", (int)r);
-    r = enc(&p->core[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, p->d.field[f], dims, strides, cb, estr,
-            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled(core) failed: %d", (int)r);
+    const int rc = encode_step_maps(p, f, p->d.field[f]);
+    if (rc != W3D_OK) return rc;
   }
   p->maps_ok = true;
   return W3D_OK;
@@ -230,14 +254,35 @@ void add_box(BoxTable* B, const int lo[3], const int hi[3]) {
   B->prefix[b + 1] = B->prefix[b] + cnt;
 }
 
-void fill_common(const W3dPlan* p, StepParams* P, int s, double a, double b, double cscale, double ct) {
+// block index -> tile index of the single-step kernel: tiles that own one of the step_depth
+// outermost layers of a face with a neighbour come first (the hardware dispatches blocks in
+// index order), so the exchange starts at the top of the kernel
+int order_step_tiles(W3dPlan* p) {
+  const Variant& v = kVariants[p->variant];
+  std::vector<int> face, rest;
+  const TileGeom& t = p->tile;
+  for (int w = 0; w < p->n_ctas; ++w) {
+    const int tx = w % t.ntx, ty = (w / t.ntx) % t.nty, ch = w / (t.ntx * t.nty);
+    const int lo[3] = {t.x0 + tx * v.tx, t.lo[1] + ty * v.ty, t.lo[2] + ch * t.zc};
+    const int hi[3] = {lo[0] + v.tx, lo[1] + v.ty, std::min(lo[2] + t.zc, t.hi[2])};
+    (face_mask_host(p->d, p->g.n, lo, hi, p->step_depth) ? face : rest).push_back(w);
+  }
+  p->n_face_ctas = (int)face.size();
+  face.insert(face.end(), rest.begin(), rest.end());
+  if (face.empty()) return W3D_OK;
+  CUDA_TRY(cudaMemcpy(p->order_dev, face.data(), face.size() * sizeof(int), cudaMemcpyHostToDevice));
+  return W3D_OK;
+}
+
+void fill_common(const W3dPlan* p, StepParams* P, int s, double a, double b, double cscale, double ct,
+                 int cur = -1, int nxt = -1) {
   std::memset(P, 0, sizeof(*P));
-  const int cur = s & 1, nxt = cur ^ 1;
+  if (cur < 0) { cur = s & 1; nxt = cur ^ 1; }
   P->map_halo = p->halo[cur];
   P->map_core = p->core[nxt];
   P->g = p->g;
-  P->cur = p->d.field[cur];
-  P->nxt = p->d.field[nxt];
+  P->cur = cur < 2 ? p->d.field[cur] : p->arr[cur];
+  P->nxt = nxt < 2 ? p->d.field[nxt] : p->arr[nxt];
   P->sx = p->d.tab[0];
   P->sy = p->d.tab[1];
   P->sz = p->d.tab[2];
@@ -250,6 +295,9 @@ void fill_common(const W3dPlan* p, StepParams* P, int s, double a, double b, dou
   P->ct_ptr = p->ct_table ? p->ct_table + (s + 1) : nullptr;
   P->status = p->d.status;
   P->level = (unsigned long long)s;
+  P->release = (unsigned long long)s + 1ull;
+  P->halo_depth = p->step_depth;
+  P->xstat = reinterpret_cast<XStat*>(static_cast<char*>(p->d.workspace) + kXStatOffset);
   P->timeout_ns = (unsigned long long)(p->d.spin_timeout_ms > 0 ? p->d.spin_timeout_ms : 10000) * 1000000ull;
 }
 
@@ -297,7 +345,19 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
   p->g.n[0] = b.n[0]; p->g.n[1] = b.n[1]; p->g.n[2] = b.n[2];
   p->g.xoff = b.xoff;
   p->g.pitch = b.pitch;
-  p->g.plane = (long long)(b.n[1] + 2) * b.pitch;
+  p->g.gs = desc->ghost_depth >= 2 ? 1 : 0;
+  p->g.plane = desc->plane_stride > 0 ? desc->plane_stride : (long long)(b.n[1] + 2) * b.pitch;
+  if (p->g.plane < (long long)(b.n[1] + 2 + 2 * p->g.gs) * b.pitch || p->g.plane % 2 != 0) {
+    delete p;
+    return fail(W3D_EINVAL, "plane_stride %lld too small for %d rows with ghost depth %d (or odd)",
+                (long long)desc->plane_stride, b.n[1], p->g.gs + 1);
+  }
+  if (p->g.gs && (desc->peer[0].active || desc->peer[1].active) && b.pitch < b.xoff + b.n[0] + 3) {
+    delete p;
+    return fail(W3D_EINVAL, "ghost depth 2 with an x neighbour needs pitch >= xoff + nx + 3 and xoff >= 2");
+  }
+  p->pair_mode = W3D_PAIR_LOCAL;
+  p->step_depth = 1;
   p->variant = desc->variant >= 0 && desc->variant < kNumVariants ? desc->variant : kDefaultVariant;
   p->num_sms = desc->num_sms;
   if (p->num_sms <= 0) {
@@ -336,26 +396,10 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
     delete p;
     return fail(W3D_EINVAL, "block needs %d CTAs, limit %d: raise zchunk", need, W3D_MAX_PARTIALS);
   }
-  // block index -> tile index: tiles that touch a face with a neighbour first (the hardware
-  // dispatches blocks in index order), so the exchange starts at the top of the kernel
   p->order_dev = reinterpret_cast<int*>(static_cast<char*>(desc->workspace) + kCounterBytes);
   {
-    std::vector<int> face, rest;
-    const TileGeom& t = p->tile;
-    for (int w = 0; w < p->n_ctas; ++w) {
-      const int tx = w % t.ntx, ty = (w / t.ntx) % t.nty, ch = w / (t.ntx * t.nty);
-      const int lo[3] = {t.x0 + tx * v.tx, t.lo[1] + ty * v.ty, t.lo[2] + ch * t.zc};
-      const int hi[3] = {lo[0] + v.tx, lo[1] + v.ty, std::min(lo[2] + t.zc, t.hi[2])};
-      (face_mask_host(*desc, p->g.n, lo, hi, 1) ? face : rest).push_back(w);
-    }
-    p->n_face_ctas = (int)face.size();
-    std::vector<int> fwd(face);
-    fwd.insert(fwd.end(), rest.begin(), rest.end());
-    cudaError_t ce = cudaMemcpy(p->order_dev, fwd.data(), fwd.size() * sizeof(int), cudaMemcpyHostToDevice);
-    if (ce != cudaSuccess) {
-      delete p;
-      return fail(W3D_ECUDA, "cudaMemcpy(order table): %s", cudaGetErrorString(ce));
-    }
+    const int rc = order_step_tiles(p);
+    if (rc != W3D_OK) { delete p; return rc; }
   }
   cudaError_t e = cudaFuncSetAttribute(v.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v.smem);
   if (e != cudaSuccess) {
@@ -387,7 +431,8 @@ int w3d_plan_init(W3dPlan* p, void* stream) { return w3d_plan_init_ex(p, stream,
 int w3d_plan_init_ex(W3dPlan* p, void* stream, int zero_second) {
   if (!p) return fail(W3D_EINVAL, "null plan");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const long long rows = (long long)(p->g.n[2] + 2) * (p->g.n[1] + 2);
+  const int gs = p->g.gs;
+  const long long rows = (long long)(p->g.n[2] + 2 + 2 * gs) * (p->g.n[1] + 2 + 2 * gs);
   const int blocks = (int)std::max<long long>(1, std::min<long long>((rows + 7) / 8, (long long)p->num_sms * 32));
   init_kernel<<<blocks, 256, 0, st>>>(p->d.field[0], zero_second ? p->d.field[1] : nullptr, p->g, p->d.tab[0],
                                       p->d.tab[1], p->d.tab[2]);
@@ -399,11 +444,10 @@ int w3d_plan_init_ex(W3dPlan* p, void* stream, int zero_second) {
   return W3D_OK;
 }
 
-int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double ct, double* err_out,
-                   void* stream) {
-  if (!p) return fail(W3D_EINVAL, "null plan");
+static int step_fused_impl(W3dPlan* p, int s, int cur, int nxt, double a, double b, double cscale, double ct,
+                           double* err_out, void* stream) {
   StepParams P;
-  fill_common(p, &P, s, a, b, cscale, ct);
+  fill_common(p, &P, s, a, b, cscale, ct, cur, nxt);
   P.err = err_ctl(p, 0, err_out);
   if (err_out && p->d.err_table && p->d.n_err_peers > 0) {
     const ptrdiff_t off = err_out - p->d.err_table;   // same offset in every rank's table
@@ -414,12 +458,11 @@ int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double 
   P.order = p->n_face_ctas > 0 ? p->order_dev : nullptr;   // identity when nothing to reorder
   P.n_face_ctas = p->n_face_ctas;
   P.use_flags = p->any_peer ? 1 : 0;
-  const int nxt = (s & 1) ^ 1;
   for (int f = 0; f < 6; ++f) {
     const W3dPeer& q = p->d.peer[f];
     P.peer[f].active = q.active;
     P.peer[f].ghost_index = q.ghost_index;
-    P.peer[f].field = q.field[nxt];
+    P.peer[f].field = nxt < 2 ? q.field[nxt] : p->peer_arr[f][nxt];
     P.peer[f].pitch = q.pitch;
     P.peer[f].plane = q.plane;
     P.peer[f].flag = q.flag;
@@ -431,6 +474,32 @@ int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double 
   P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
   return launch_fused(p, P, p->n_ctas, static_cast<cudaStream_t>(stream));
 }
+
+int w3d_step_fused(W3dPlan* p, int s, double a, double b, double cscale, double ct, double* err_out,
+                   void* stream) {
+  if (!p) return fail(W3D_EINVAL, "null plan");
+  return step_fused_impl(p, s, s & 1, (s & 1) ^ 1, a, b, cscale, ct, err_out, stream);
+}
+
+int w3d_step_fused_on(W3dPlan* p, int s, int cur, int prev, double a, double b, double cscale, double ct,
+                      double* err_out, void* stream) {
+  if (!p) return fail(W3D_EINVAL, "null plan");
+  if (cur < 0 || cur > 3 || prev < 0 || prev > 3 || cur == prev) return fail(W3D_EINVAL, "bad array indices");
+  if ((cur > 1 || prev > 1) && !p->pair_ready) return fail(W3D_EINVAL, "arrays 2, 3 exist after w3d_plan_enable_pairs only");
+  return step_fused_impl(p, s, cur, prev, a, b, cscale, ct, err_out, stream);
+}
+
+int w3d_plan_exchange_stats(W3dPlan* p, unsigned long long out[W3D_XSTAT_WORDS], void* stream) {
+  if (!p || !out) return fail(W3D_EINVAL, "null argument");
+  XStat h;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUDA_TRY(cudaMemcpyAsync(&h, static_cast<char*>(p->d.workspace) + kXStatOffset, sizeof(h), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  out[0] = h.sum_wait; out[1] = h.sum_copy; out[2] = h.launches; out[3] = h.max_wait; out[4] = h.max_copy;
+  return W3D_OK;
+}
+
+int w3d_plan_pair_mode(W3dPlan* p) { return p ? p->pair_mode : W3D_PAIR_LOCAL; }
 
 int w3d_step_tma(W3dPlan* p, int s, double a, double b, double cscale, double ct, const int32_t lo[3],
                  const int32_t hi[3], double* err_out, int slot, void* stream) {
@@ -484,58 +553,88 @@ int w3d_step_box(W3dPlan* p, int s, double a, double b, double cscale, double ct
   return W3D_OK;
 }
 
-int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const* peer_aux, int pair_variant,
-                          int zchunk) {
-  if (!p || !aux0 || !aux1) return fail(W3D_EINVAL, "null argument");
-  if ((reinterpret_cast<uintptr_t>(aux0) | reinterpret_cast<uintptr_t>(aux1)) & 15)
-    return fail(W3D_EINVAL, "aux arrays must be 16-byte aligned");
-  EncodeTiledFn enc = get_encode();
-  if (!enc) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled is not available from the driver");
-  p->pair_variant = pair_variant >= 0 && pair_variant < kNumPairVariants ? pair_variant : 4;   // best of the measured sweep
-  const PairVariant& v = kPairVariants[p->pair_variant];
-  p->arr[0] = p->d.field[0]; p->arr[1] = p->d.field[1]; p->arr[2] = aux0; p->arr[3] = aux1;
-  const cuuint64_t dims[3] = {(cuuint64_t)p->g.pitch, (cuuint64_t)(p->g.n[1] + 2), (cuuint64_t)(p->g.n[2] + 2)};
-  const cuuint64_t strides[2] = {(cuuint64_t)p->g.pitch * 8, (cuuint64_t)p->g.plane * 8};
-  const cuuint32_t estr[3] = {1, 1, 1};
-  const cuuint32_t ab[3] = {(cuuint32_t)(v.tx + 4), (cuuint32_t)(v.ty + 4), 1};
-  const cuuint32_t bb[3] = {(cuuint32_t)(v.tx + 4), (cuuint32_t)(v.ty + 2), 1};
-  for (int f = 0; f < 4; ++f) {
-    CUresult r = enc(&p->pmap_a[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, p->arr[f], dims, strides, ab, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled(pair A) failed: %d", (int)r);
-    r = enc(&p->pmap_b[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, p->arr[f], dims, strides, bb, estr,
-            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(W3D_EDRIVER, "cuTensorMapEncodeTiled(pair B) failed: %d", (int)r);
-  }
-  CUDA_TRY(cudaFuncSetAttribute(v.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v.smem));
-  // tile geometry over the whole block (one CTA per SM; chunk cost includes 4 extra planes)
-  TileGeom& t = p->ptile;
+// per-CTA cost of a pair pass in "plane units" for a tile of ty rows and zc planes: zc planes of
+// work plus 4 halo planes that are loaded and partly computed, plus a fixed fill / drain term
+static double pair_cta_cost(int ty, int zc) { return (double)ty / 32.0 * (zc + 4.0 * 0.45 + 2.0); }
+
+// tile geometry of pair variant `vi` over the whole block; returns the modelled pass cost
+static double plan_pair_tiles(const W3dPlan* p, int vi, int zchunk, TileGeom* out) {
+  const PairVariant& v = kPairVariants[vi];
+  TileGeom t;
   for (int d = 0; d < 3; ++d) { t.lo[d] = 1; t.hi[d] = p->g.n[d] + 1; }
   t.x0 = 1 - ((p->g.xoff + 1) & 1);
   t.ntx = (t.hi[0] - t.x0 + v.tx - 1) / v.tx;
   t.nty = (p->g.n[1] + v.ty - 1) / v.ty;
   const int ez = p->g.n[2];
   const long long tiles = (long long)t.ntx * t.nty;
+  const long long slots = (long long)p->num_sms * v.ctas_per_sm;
+  double best = 1e300;
   if (zchunk > 0) {
     t.zc = std::min(std::min(zchunk, ez), 636);
+    const long long ctas = tiles * ((ez + t.zc - 1) / t.zc);
+    best = (double)((ctas + slots - 1) / slots) * pair_cta_cost(v.ty, t.zc);
   } else {
-    double best = 1e300;
     int best_c = std::max(1, (ez + 635) / 636);
     for (int c = 1; c <= std::max(1, ez / 16); ++c) {
       const int zc = (ez + c - 1) / c;
       if (zc + 4 > 640) continue;                 // the kernel stages zc+4 table entries in shared memory
       const long long ctas = tiles * ((ez + zc - 1) / zc);
       if (ctas > W3D_MAX_PARTIALS) break;
-      const long long slots = (long long)p->num_sms * v.ctas_per_sm;
       const long long waves = (ctas + slots - 1) / slots;
-      const double cost = (double)waves * (zc + 4.0 * 0.45 + 2.0);
+      const double cost = (double)waves * pair_cta_cost(v.ty, zc);
       if (cost < best - 1e-9) { best = cost; best_c = c; }
     }
     t.zc = (ez + best_c - 1) / best_c;
   }
   t.nchunks = (ez + t.zc - 1) / t.zc;
+  *out = t;
+  return best;
+}
+
+int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const* peer_aux, int pair_variant,
+                          int zchunk) {
+  if (!p || !aux0 || !aux1) return fail(W3D_EINVAL, "null argument");
+  if ((reinterpret_cast<uintptr_t>(aux0) | reinterpret_cast<uintptr_t>(aux1)) & 15)
+    return fail(W3D_EINVAL, "aux arrays must be 16-byte aligned");
+  p->arr[0] = p->d.field[0]; p->arr[1] = p->d.field[1]; p->arr[2] = aux0; p->arr[3] = aux1;
+  // protocol for faces with a neighbour (see wave3d.h)
+  int active_axes = 0;
+  for (int d = 0; d < 3; ++d) active_axes += (p->d.peer[d * 2].active || p->d.peer[d * 2 + 1].active) ? 1 : 0;
+  p->pair_mode = active_axes == 0 ? W3D_PAIR_LOCAL : (p->g.gs == 1 && active_axes == 1) ? W3D_PAIR_WIDE : W3D_PAIR_FIXUP;
+  if (p->pair_mode == W3D_PAIR_WIDE)
+    for (int d = 0; d < 3; ++d)
+      if ((p->d.peer[d * 2].active || p->d.peer[d * 2 + 1].active) && p->g.n[d] < 2)
+        return fail(W3D_EINVAL, "wide halo needs at least 2 unknowns along the axis with neighbours");
+  // variant: given, or the cheaper of the measured 64x32 default and the 64x30 tiling by the wave model
+  // (64x30 only wins when it removes a partial wave, e.g. 511 rows: 16 -> 18 tiles, 128 -> 144 CTAs)
+  if (pair_variant >= 0 && pair_variant < kNumPairVariants) {
+    p->pair_variant = pair_variant;
+    plan_pair_tiles(p, p->pair_variant, zchunk, &p->ptile);
+  } else {
+    const int cand[2] = {4, 8};
+    double best = 1e300;
+    for (int c = 0; c < 2; ++c) {
+      TileGeom t;
+      const double cost = plan_pair_tiles(p, cand[c], zchunk, &t) * (c == 0 ? 1.0 : 1.03);   // ties and near-ties: keep the default
+      if (cost < best) { best = cost; p->pair_variant = cand[c]; p->ptile = t; }
+    }
+  }
+  if (p->pair_mode == W3D_PAIR_WIDE && p->step_depth != 2) {
+    // the single-step kernel keeps the wide halo alive too (it ships two layers), so single steps
+    // and pair passes can follow each other in any order
+    p->step_depth = 2;
+    const int rc = order_step_tiles(p);
+    if (rc != W3D_OK) return rc;
+  }
+  const PairVariant& v = kPairVariants[p->pair_variant];
+  for (int f = 0; f < 4; ++f) {
+    int rc = encode_one(p, &p->pmap_a[f], p->arr[f], v.tx + 4, v.ty + 4, p->g.gs, "pair A");
+    if (rc == W3D_OK) rc = encode_one(p, &p->pmap_b[f], p->arr[f], v.tx + 4, v.ty + 2, p->g.gs, "pair B");
+    if (rc == W3D_OK && f >= 2) rc = encode_step_maps(p, f, p->arr[f]);
+    if (rc != W3D_OK) return rc;
+  }
+  CUDA_TRY(cudaFuncSetAttribute(v.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, v.smem));
+  TileGeom& t = p->ptile;
   p->pn_ctas = t.ntx * t.nty * t.nchunks;
   if (p->pn_ctas > W3D_MAX_PARTIALS) return fail(W3D_EINVAL, "pair kernel needs %d CTAs, limit %d", p->pn_ctas, W3D_MAX_PARTIALS);
   // neighbours' arrays by index; face CTAs first in the block -> tile table of the pair kernel
@@ -548,14 +647,16 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const*
       return fail(W3D_EINVAL, "face %d has a neighbour but no peer aux arrays were given", f);
   }
   {
-    // order: tiles that own an edge layer (they wait, copy out and are counted for the release),
-    // then tiles that only read a ghost layer through their level-1 ring (they wait), then the rest
+    // order: tiles that copy halo layers out (they wait, copy and are counted for the release),
+    // then tiles that only read a ghost layer through their level-1 ring (they wait), then the rest.
+    // Wide halo: two layers are shipped, so both sets are the tiles within 2 layers of a face.
+    const int depth = p->pair_mode == W3D_PAIR_WIDE ? 2 : 1;
     std::vector<int> face, waiters, rest;
     for (int w = 0; w < p->pn_ctas; ++w) {
       const int tx = w % t.ntx, ty = (w / t.ntx) % t.nty, ch = w / (t.ntx * t.nty);
       const int lo[3] = {t.x0 + tx * v.tx, t.lo[1] + ty * v.ty, t.lo[2] + ch * t.zc};
       const int hi[3] = {lo[0] + v.tx, lo[1] + v.ty, std::min(lo[2] + t.zc, t.hi[2])};
-      if (face_mask_host(p->d, p->g.n, lo, hi, 1)) face.push_back(w);
+      if (face_mask_host(p->d, p->g.n, lo, hi, depth)) face.push_back(w);
       else if (face_mask_host(p->d, p->g.n, lo, hi, 2)) waiters.push_back(w);
       else rest.push_back(w);
     }
@@ -567,8 +668,10 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const*
   }
   p->pair_ready = true;
   const size_t used = std::strlen(p->text);
-  snprintf(p->text + used, sizeof(p->text) - used, " || %s (%d thr, %d B smem): tiles %dx%d zc %d chunks %d -> %d CTAs",
-           v.name, v.threads, v.smem, t.ntx, t.nty, t.zc, t.nchunks, p->pn_ctas);
+  static const char* kModeName[3] = {"no neighbours", "wide halo: 1 launch + 1 handshake per 2 steps", "fix-up pass: 2 launches per 2 steps"};
+  snprintf(p->text + used, sizeof(p->text) - used,
+           " || %s (%d thr, %d B smem): tiles %dx%d zc %d chunks %d -> %d CTAs, %d face CTAs [%s]", v.name, v.threads,
+           v.smem, t.ntx, t.nty, t.zc, t.nchunks, p->pn_ctas, p->pn_face_ctas, kModeName[p->pair_mode]);
   return W3D_OK;
 }
 
@@ -593,6 +696,7 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
       if (idx[i] == idx[j]) return fail(W3D_EINVAL, "the four arrays of a pair step must be distinct");
   }
   const PairVariant& v = kPairVariants[p->pair_variant];
+  const bool wide = p->pair_mode == W3D_PAIR_WIDE;
   PairParams P;
   std::memset(&P, 0, sizeof(P));
   P.map_a = p->pmap_a[cur];
@@ -612,19 +716,26 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
   set_bcast(p, &P.err2, err2);
   P.tile = p->ptile;
   P.order = p->pn_face_ctas > 0 ? p->order_dev + W3D_MAX_PARTIALS : nullptr;   // identity when nothing to reorder
+  P.wide = wide ? 1 : 0;
   for (int d = 0; d < 3; ++d) {
-    P.skip_lo[d] = p->d.peer[d * 2].active ? 1 : 0;
-    P.skip_hi[d] = p->d.peer[d * 2 + 1].active ? 1 : 0;
+    const int lo_act = p->d.peer[d * 2].active ? 1 : 0, hi_act = p->d.peer[d * 2 + 1].active ? 1 : 0;
+    P.skip_lo[d] = wide ? 0 : lo_act;
+    P.skip_hi[d] = wide ? 0 : hi_act;
+    P.in_lo[d] = 1 - (wide ? lo_act : 0);
+    P.in_hi[d] = p->g.n[d] + (wide ? hi_act : 0);
   }
-  // fused exchange of level s+1 (the array out1)
-  P.nxt = p->arr[out1];
+  // fused exchange: level s+1 (array out1, one layer) with the fix-up protocol,
+  // level s+2 (array out2, two layers) with the wide halo
+  const int ship = wide ? out2 : out1;
+  P.nxt = p->arr[ship];
+  P.halo_depth = wide ? 2 : 1;
   P.n_face_ctas = p->pn_face_ctas;
   P.use_flags = p->any_peer ? 1 : 0;
   for (int f = 0; f < 6; ++f) {
     const W3dPeer& q = p->d.peer[f];
     P.peer[f].active = q.active;
     P.peer[f].ghost_index = q.ghost_index;
-    P.peer[f].field = p->peer_arr[f][out1];
+    P.peer[f].field = p->peer_arr[f][ship];
     P.peer[f].pitch = q.pitch;
     P.peer[f].plane = q.plane;
     P.peer[f].flag = q.flag;
@@ -632,7 +743,9 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
   P.flags_in = p->d.flags_in;
   P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
   P.status = p->d.status;
+  P.xstat = reinterpret_cast<XStat*>(static_cast<char*>(p->d.workspace) + kXStatOffset);
   P.level = (unsigned long long)s;
+  P.release = (unsigned long long)s + (wide ? 2ull : 1ull);
   P.timeout_ns = (unsigned long long)(p->d.spin_timeout_ms > 0 ? p->d.spin_timeout_ms : 10000) * 1000000ull;
   v.kernel<<<p->pn_ctas, v.threads, v.smem, static_cast<cudaStream_t>(stream)>>>(P);
   CUDA_TRY(cudaGetLastError());
@@ -645,6 +758,7 @@ int w3d_step_fixup(W3dPlan* p, int level, int cur, int prev, int out, double a, 
   if (!p || !p->pair_ready) return fail(W3D_EINVAL, "w3d_plan_enable_pairs has not been called");
   if (cur < 0 || cur > 3 || prev < 0 || prev > 3 || out < 0 || out > 3 || cur == out || prev == out)
     return fail(W3D_EINVAL, "bad array indices");
+  if (p->pair_mode != W3D_PAIR_FIXUP) return fail(W3D_EINVAL, "this plan's pair passes need no fix-up (w3d_plan_pair_mode)");
   const long long nodes = p->shell.prefix[p->shell.nboxes];
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (nodes == 0) {
@@ -652,7 +766,7 @@ int w3d_step_fixup(W3dPlan* p, int level, int cur, int prev, int out, double a, 
     return W3D_OK;
   }
   StepParams P;
-  fill_common(p, &P, level, a, b, cscale, ct);   // (sets ct_ptr = ct_table + level + 1 when a table is attached)
+  fill_common(p, &P, level, a, b, cscale, ct, 0, 1);   // (sets ct_ptr = ct_table + level + 1 when a table is attached)
   P.cur = p->arr[cur];
   P.nxt = p->arr[out];
   P.prev_sep = p->arr[prev];

@@ -29,6 +29,7 @@ extern "C" {
 #define W3D_ECUDA (-2)
 #define W3D_ENOMEM (-3)
 #define W3D_EDRIVER (-4)
+#define W3D_ETOOBIG (-5)     /* w3d_error_norms_noalloc only: block exceeds the built-in scratch */
 
 #define W3D_XOFF 15          /* x ghost sits at element 15, first unknown at 16 (128 B aligned) */
 #define W3D_PITCH_ALIGN 16   /* row pitch is a multiple of 16 doubles (128 B) */
@@ -72,6 +73,14 @@ typedef struct W3dPlanDesc {
   double* err_table;
   double* err_table_peer[7];
   int32_t n_err_peers;
+  /* Ghost depth of the field arrays (0 or 1: one ghost layer, the classic layout; 2: two).
+   * With 2, field[] (and the aux arrays of w3d_plan_enable_pairs, and the peers' arrays) point at
+   * local index (0,0,0) of an allocation that also holds rows / planes -1 and n+2 (and columns
+   * xoff-1, xoff+n+2 when an x face has a neighbour), plane_stride >= (ny+4)*pitch, and the
+   * tables tab[d] are readable at indices -1 and n+2 (0 beyond a Dirichlet boundary).  This is
+   * what lets two time steps share ONE launch and ONE halo handshake (see w3d_step_pair). */
+  int32_t ghost_depth;
+  int64_t plane_stride;         /* elements between planes; 0 = (ny+2)*pitch */
 } W3dPlanDesc;
 
 typedef struct W3dPlan W3dPlan;
@@ -130,15 +139,28 @@ int w3d_step_box(W3dPlan* plan, int s, double a, double b, double cscale, double
  * arrays of the same layout; the four arrays are addressed by index: 0,1 = desc.field[0..1],
  * 2,3 = aux0, aux1.  w3d_step_pair reads level n from `cur` and level n-1 from `prev` and
  * writes level n+1 to `out1` and level n+2 to `out2` (all four distinct).  (a,b,cscale,ct)
- * are given per produced level.  Nodes next to a face that has a neighbour are left out of
- * `out2` (their level-n+1 ghost is not known inside the pass); the caller finishes them
- * with w3d_step_fixup after the exchange of level n+1.  peer_aux: for every face f with a
- * neighbour, peer_aux[2f] and peer_aux[2f+1] are that neighbour's aux0/aux1 mapped here. */
+ * are given per produced level.  peer_aux: for every face f with a neighbour, peer_aux[2f]
+ * and peer_aux[2f+1] are that neighbour's aux0/aux1 mapped here.
+ *
+ * Faces with a neighbour — w3d_plan_pair_mode() tells which protocol the plan uses:
+ *   W3D_PAIR_LOCAL  no face has a neighbour: nothing to exchange.
+ *   W3D_PAIR_WIDE   ghost_depth 2 and neighbours along at most one axis: ONE launch and ONE
+ *       handshake per two steps.  `cur` must hold two valid ghost layers and `prev` one; the
+ *       pass also forms level n+1 on the first ghost layer (kept in out1's ghosts for the next
+ *       pass), completes level n+2 on every owned node, ships its two outermost layers per face
+ *       into the neighbours' ghost layers of their `out2` and releases level s+2.
+ *   W3D_PAIR_FIXUP  otherwise (one ghost layer, or neighbours along two or three axes — the
+ *       wide scheme would also need the edge lines of the diagonal neighbours): nodes next to a
+ *       face with a neighbour are left out of `out2`; the pass ships level n+1 (one layer,
+ *       releases s+1) and the caller finishes the layer with w3d_step_fixup. */
+#define W3D_PAIR_LOCAL 0
+#define W3D_PAIR_WIDE 1
+#define W3D_PAIR_FIXUP 2
 int w3d_plan_enable_pairs(W3dPlan* plan, double* aux0, double* aux1, double* const* peer_aux /* [12] or NULL */,
                           int pair_variant, int zchunk);
-/* s = level held by `cur`.  Face CTAs acquire the neighbours' flags for level s, and after
- * their tile is written they copy the level-(s+1) face layers of `out1` into the neighbours'
- * ghost layers; the last one releases level s+1. */
+int w3d_plan_pair_mode(W3dPlan* plan);
+/* s = level held by `cur`.  Face CTAs acquire the neighbours' flags for level s before their
+ * first load; see the protocols above for what they ship afterwards. */
 int w3d_step_pair(W3dPlan* plan, int s, int cur, int prev, int out1, int out2, double a1, double b1,
                   double cscale1, double ct1, double a2, double b2, double cscale2, double ct2, double* err1,
                   double* err2, void* stream);
@@ -148,6 +170,22 @@ int w3d_step_pair(W3dPlan* plan, int s, int cur, int prev, int out1, int out2, d
  * the local array and into the neighbours' ghost layers; releases level + 1. */
 int w3d_step_fixup(W3dPlan* plan, int level, int cur, int prev, int out, double a, double b, double cscale,
                    double ct, double* err_out, void* stream);
+
+/* Single step on any two of the four arrays (after w3d_plan_enable_pairs): same kernel and
+ * protocol as w3d_step_fused, with level s in array `cur` and level s-1 in array `prev`, which
+ * receives level s+1.  Used for the last step of an odd-length run in pair mode. */
+int w3d_step_fused_on(W3dPlan* plan, int s, int cur, int prev, double a, double b, double cscale, double ct,
+                      double* err_out, void* stream);
+
+/* Exchange statistics measured on the device (%globaltimer, nanoseconds): how long face CTAs
+ * spun on their neighbours' flags and how long their halo copy-out (P2P stores + system fence)
+ * took.  Per launch the maximum over the face CTAs is taken; out[] receives
+ *   [0] sum over launches of the flag-wait maxima   [1] sum of the copy-out maxima
+ *   [2] launches counted   [3] largest single flag wait   [4] largest single copy-out.
+ * Counterpart of the reference's "MPI" and "H2D/D2H" time columns (report.pdf p.16 §4.4).
+ * Synchronises the stream it is given.  w3d_plan_init clears the counters. */
+#define W3D_XSTAT_WORDS 5
+int w3d_plan_exchange_stats(W3dPlan* plan, unsigned long long out[W3D_XSTAT_WORDS], void* stream);
 
 /* NCCL-baseline helpers (K5): contiguous face buffers of the unknowns of the two
  * other axes, fastest index first.  ghost=0 packs/unpacks the edge layer of
@@ -179,7 +217,6 @@ int w3d_error_norms(const double* u, const W3dBlock* blk, const double* sx, cons
  * ordered on one stream are fine, calls that may overlap on the GPU race.  On failure
  * the reason is written to errbuf (may be NULL).  out[0] = max error, out[1] = sum of
  * squares, as for w3d_error_norms (the sum may differ in the last bits: other order). */
-#define W3D_ETOOBIG (-5)
 #define W3D_NOALLOC_MAX_ROWS 262144
 #define W3D_NOALLOC_SCRATCH_BYTES 33024
 int w3d_error_norms_noalloc(const double* u, const W3dBlock* blk, const double* sx, const double* sy,

@@ -36,7 +36,7 @@ class W3dPlanDesc(C.Structure):
                 ("status", C.c_void_p), ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
                 ("variant", C.c_int32), ("zchunk", C.c_int32), ("num_sms", C.c_int32),
                 ("spin_timeout_ms", C.c_int32), ("err_table", C.c_void_p), ("err_table_peer", C.c_void_p * 7),
-                ("n_err_peers", C.c_int32)]
+                ("n_err_peers", C.c_int32), ("ghost_depth", C.c_int32), ("plane_stride", C.c_int64)]
 
 
 class CudaLibError(RuntimeError):
@@ -65,6 +65,9 @@ def lib() -> C.CDLL:
     l.w3d_plan_init_ex.argtypes = [vp, vp, C.c_int]
     l.w3d_plan_set_ct_table.argtypes = [vp, vp]
     l.w3d_step_fused.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
+    l.w3d_step_fused_on.argtypes = [vp, C.c_int, C.c_int, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
+    l.w3d_plan_pair_mode.argtypes = [vp]
+    l.w3d_plan_exchange_stats.argtypes = [vp, C.POINTER(C.c_ulonglong), vp]
     l.w3d_step_tma.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, i32p, i32p, vp, C.c_int, vp]
     l.w3d_step_box.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, i32p, i32p, vp, C.c_int, vp]
     l.w3d_plan_enable_pairs.argtypes = [vp, vp, vp, C.POINTER(vp), C.c_int, C.c_int]
@@ -82,21 +85,34 @@ def check(rc: int) -> None:
         raise CudaLibError(f"libwave3d_b200 error {rc}: {lib().w3d_last_error().decode()}")
 
 
-def pitch_for(nx: int) -> int:
-    need = XOFF + nx + 2
+PAIR_LOCAL, PAIR_WIDE, PAIR_FIXUP = 0, 1, 2      # w3d_plan_pair_mode()
+
+
+def pitch_for(nx: int, x_ghosts: int = 1) -> int:
+    """Row pitch (elements) for nx unknowns and `x_ghosts` ghost columns per side."""
+    need = XOFF + nx + 1 + x_ghosts
     return (need + PITCH_ALIGN - 1) // PITCH_ALIGN * PITCH_ALIGN
 
 
-def make_block(n: Sequence[int]) -> W3dBlock:
+def make_block(n: Sequence[int], pitch: int = 0) -> W3dBlock:
     b = W3dBlock()
     b.n[:] = list(n)
     b.xoff = XOFF
-    b.pitch = pitch_for(n[0])
+    b.pitch = pitch or pitch_for(n[0])
     return b
 
 
 def field_shape(n: Sequence[int]) -> Tuple[int, int, int]:
     return (n[2] + 2, n[1] + 2, pitch_for(n[0]))
+
+
+def wide_alloc_shape(n: Sequence[int], x_wide: bool = False) -> Tuple[int, int, int]:
+    """Allocation with TWO ghost layers per side in y and z (and x when ``x_wide``).
+
+    The library is handed the view ``alloc[1:-1, 1:-1]`` — local index (0,0,0) as in the classic
+    layout, explicit plane stride — so every kernel written for one ghost layer runs on it
+    unchanged, and the two-steps-per-pass kernel reaches rows / planes -1 and n+2."""
+    return (n[2] + 4, n[1] + 4, pitch_for(n[0], 2 if x_wide else 1))
 
 
 def stream_ptr() -> int:
@@ -129,19 +145,29 @@ class CudaPlan:
                  coef: Sequence[float], flags_in: torch.Tensor, status: torch.Tensor,
                  workspace: torch.Tensor, peers: Optional[dict] = None, variant: int = -1,
                  zchunk: int = 0, spin_timeout_ms: int = 0, err_table_ptr: int = 0,
-                 err_table_peer_ptrs: Sequence[int] = ()):
+                 err_table_peer_ptrs: Sequence[int] = (), ghost_depth: int = 1):
+        """fields: two tensors of shape (nz+2, ny+2, pitch).  With ``ghost_depth=2`` they are the
+        ``[1:-1, 1:-1]`` views of allocations made with :func:`wide_alloc_shape`, and the tables
+        are the ``[1:-1]`` views of tables with n+4 entries."""
         self.n = tuple(int(x) for x in n)
-        self.blk = make_block(self.n)
         self.fields = list(fields)
         self.tables = list(tables)
         self.flags_in, self.status, self.workspace = flags_in, status, workspace
-        shape = field_shape(self.n)
+        self.ghost_depth = ghost_depth
+        f0 = self.fields[0]
+        pitch, plane = int(f0.stride(1)), int(f0.stride(0))
+        self.blk = make_block(self.n, pitch)
         for f in self.fields:
-            assert f.is_cuda and f.dtype == torch.float64 and tuple(f.shape) == shape and f.is_contiguous()
+            assert f.is_cuda and f.dtype == torch.float64 and tuple(f.shape[:2]) == (self.n[2] + 2, self.n[1] + 2)
+            assert f.stride(2) == 1 and f.stride(1) == pitch and f.stride(0) == plane and f.shape[2] == pitch
+            if ghost_depth < 2:
+                assert f.is_contiguous()
         for t, nn in zip(self.tables, self.n):
             assert t.is_cuda and t.dtype == torch.float64 and t.numel() == nn + 2
         d = W3dPlanDesc()
         d.blk = self.blk
+        d.ghost_depth = ghost_depth
+        d.plane_stride = plane
         d.field[0], d.field[1] = self.fields[0].data_ptr(), self.fields[1].data_ptr()
         for k in range(3):
             d.tab[k] = self.tables[k].data_ptr()
@@ -215,12 +241,30 @@ class CudaPlan:
 
         peer_aux: face index -> (aux0 address, aux1 address) of that neighbour's arrays."""
         for a in (aux0, aux1):
-            assert a.is_cuda and a.dtype == torch.float64 and a.shape == self.fields[0].shape and a.is_contiguous()
+            assert a.is_cuda and a.dtype == torch.float64 and a.shape == self.fields[0].shape
+            assert a.stride() == self.fields[0].stride()
         self.aux = [aux0, aux1]
         table = (C.c_void_p * 12)()
         for f, (p0, p1) in (peer_aux or {}).items():
             table[2 * f], table[2 * f + 1] = p0, p1
         check(lib().w3d_plan_enable_pairs(self._h, aux0.data_ptr(), aux1.data_ptr(), table, pair_variant, zchunk))
+
+    @property
+    def pair_mode(self) -> int:
+        """PAIR_LOCAL / PAIR_WIDE / PAIR_FIXUP: how pair passes treat faces with a neighbour."""
+        return int(lib().w3d_plan_pair_mode(self._h))
+
+    def step_fused_on(self, s: int, cur: int, prev: int, a: float, b: float, cscale: float, ct: float,
+                      err_out: Optional[torch.Tensor] = None) -> None:
+        """Single step with level s in array `cur` and level s-1 in array `prev` (overwritten)."""
+        check(lib().w3d_step_fused_on(self._h, s, cur, prev, a, b, cscale, ct, self._err_ptr(err_out), stream_ptr()))
+
+    def exchange_stats(self) -> dict:
+        """Device-measured exchange time since init (see w3d_plan_exchange_stats); synchronises."""
+        out = (C.c_ulonglong * 5)()
+        check(lib().w3d_plan_exchange_stats(self._h, out, stream_ptr()))
+        return {"flag_wait_s": out[0] * 1e-9, "halo_copy_s": out[1] * 1e-9, "launches": int(out[2]),
+                "max_flag_wait_s": out[3] * 1e-9, "max_halo_copy_s": out[4] * 1e-9}
 
     def step_pair(self, s: int, cur: int, prev: int, out1: int, out2: int, lvl1, lvl2, err1=None, err2=None) -> None:
         """s = level held by array `cur`; lvl1 / lvl2 = (a, b, cscale, ct) of the two produced levels."""

@@ -141,19 +141,24 @@ def plan_all(p: WaveProblem, dims: Sequence[int]) -> List[RankBlock]:
     return [plan_rank(p, dims, r) for r in range(world)]
 
 
-def local_tables(p: WaveProblem, blk: RankBlock) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
-    """Per-axis analytic tables for the local block *including ghosts* (n+2 entries).
+def local_tables(p: WaveProblem, blk: RankBlock, ghosts: int = 1) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """Per-axis analytic tables for the local block *including ghosts* (n + 2*ghosts entries).
 
-    Entry l corresponds to global node ``lo - 1 + l`` (wrapped on periodic axes).
+    Entry l corresponds to global node ``lo - ghosts + l`` (wrapped on periodic axes; 0 for
+    nodes beyond a Dirichlet boundary, which only a second ghost layer can reach).
     Values are taken from the global table so that every decomposition sees
     bit-identical numbers.
     """
     out = []
     for d in range(3):
-        g = np.arange(blk.lo[d] - 1, blk.lo[d] + blk.n[d] + 1)
+        g = np.arange(blk.lo[d] - ghosts, blk.lo[d] + blk.n[d] + ghosts)
+        full = axis_table(p, d)
         if p.periodic[d]:
-            g = np.mod(g, p.N[d])
-        out.append(np.ascontiguousarray(axis_table(p, d)[g]))
+            t = full[np.mod(g, p.N[d])]
+        else:
+            inside = (g >= 0) & (g <= p.N[d])
+            t = np.where(inside, full[np.clip(g, 0, p.N[d])], 0.0)
+        out.append(np.ascontiguousarray(t))
     return tuple(out)
 
 

@@ -15,9 +15,9 @@ MPI, here:
   * the error max / sum-of-squares is an epilogue of the same kernels, and the
     last CTA stores the pair into every rank's table, so after the loop each rank
     already holds all partials (no collective at all);
-  * by default two time steps share one pass over memory (``pair=True``:
-    ``w3d_step_pair`` + ``w3d_step_fixup``); ``pair=False`` runs
-    one ``w3d_step_fused`` launch per step;
+  * by default two time steps share one pass over memory AND one launch AND one
+    halo handshake (``pair=True``: ``w3d_step_pair`` on arrays with two ghost
+    layers, DESIGN.md §4b); ``pair=False`` runs one ``w3d_step_fused`` launch per step;
   * the K steps of a run are captured in one CUDA graph.
 
 With world size 1 the same code runs on plain device tensors (a periodic axis
@@ -42,18 +42,36 @@ _FLAG_BYTES = 256     # 6 flag words + padding, at the head of the symmetric buf
 _SLOTS = 2            # error-table entries per rank and level (step kernel, fix-up pass)
 
 
-def _field_bytes(n: Sequence[int]) -> int:
-    a, b, c = cuda.field_shape(n)
-    return a * b * c * 8
+class _Layout:
+    """Where the arrays of one rank's block sit inside its (symmetric) buffer.
+
+    ``wide`` (pair mode): every array is allocated with two ghost layers per side in y and z
+    (x as well when an x face has a neighbour) and the library works on the ``[1:-1, 1:-1]``
+    view, so local index (0,0,0) and the ghost-depth-1 kernels are unchanged while the
+    two-steps-per-pass kernel reaches rows / planes -1 and n+2."""
+
+    def __init__(self, n: Sequence[int], wide: bool, x_wide: bool):
+        self.n = tuple(n)
+        self.wide = wide
+        self.shape = cuda.wide_alloc_shape(n, x_wide) if wide else cuda.field_shape(n)
+        self.pitch = self.shape[2]
+        self.plane = self.shape[1] * self.shape[2]
+        self.nbytes = self.shape[0] * self.plane * 8
+        self.origin = (self.plane + self.pitch) * 8 if wide else 0     # byte offset of local index (0,0,0)
+
+    def view(self, alloc: torch.Tensor) -> torch.Tensor:
+        return alloc[1:-1, 1:-1] if self.wide else alloc
 
 
 class FusedSolver:
     def __init__(self, p: WaveProblem, dims: Sequence[int] = (1, 1, 1), device: Optional[torch.device] = None,
                  group=None, every: int = 2, variant: int = -1, zchunk: int = 0, use_graph: bool = True,
-                 spin_timeout_ms: int = 0, pair: bool = False, pair_variant: int = -1):
+                 spin_timeout_ms: int = 0, pair: bool = True, pair_variant: int = -1):
         self._launches_per_run = p.K
-        # pair mode with an even K never reads array 1 before overwriting it
-        self._zero_second = not (pair and p.K % 2 == 0)
+        self.pair = bool(pair)
+        # pair mode never reads array 1 before overwriting it (the first pass skips the previous
+        # level, DESIGN.md §4b) unless the whole run is the single Taylor step
+        self._zero_second = not (self.pair and p.K >= 2)
         self.p, self.dims, self.every = p, tuple(int(d) for d in dims), every
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -65,13 +83,14 @@ class FusedSolver:
         blocks = plan_all(p, self.dims)
         self.blk = blocks[self.rank]
         blk = self.blk
-        fbytes = max(_field_bytes(b.n) for b in blocks)
-        fbytes = (fbytes + 255) // 256 * 256
+        x_wide = self.pair and any(b.nbr[0][s] >= 0 for b in blocks for s in range(2))
+        lay = [_Layout(b.n, self.pair, x_wide) for b in blocks]
+        self.lay = lay[self.rank]
+        fbytes = (max(l.nbytes for l in lay) + 255) // 256 * 256
         # error table: one row per rank, (K+1) x (max, sum sq); every rank holds a full copy
         # that the other ranks' kernels fill over NVLink
         tbytes = (self.world * (p.K + 1) * _SLOTS * 16 + 255) // 256 * 256
         f0 = _FLAG_BYTES + tbytes                     # offset of the first field array
-        self.pair = bool(pair)
         narr = 4 if self.pair else 2                  # temporal blocking needs two more arrays
         total = f0 + narr * fbytes
         # ---- storage: symmetric when there are real peers ----
@@ -86,17 +105,19 @@ class FusedSolver:
             base_ptrs = [buf.data_ptr()]
         buf.zero_()
         self.buf = buf
-        shape = cuda.field_shape(blk.n)
-        nel = shape[0] * shape[1] * shape[2]
+        nel = self.lay.shape[0] * self.lay.plane
         self.flags = buf[:_FLAG_BYTES].view(torch.int64)
-        self.f = [buf[f0 + q * fbytes: f0 + q * fbytes + nel * 8].view(torch.float64).view(shape)
-                  for q in range(2)]
-        self.aux = [buf[f0 + q * fbytes: f0 + q * fbytes + nel * 8].view(torch.float64).view(shape)
-                    for q in range(2, narr)]
-        # (world, K+1, slots, 2): slot 0/1 = the step kernels, slot 1 also = the fix-up pass of a pair
+        # whole allocations (all ghost layers) and the views the library works on
+        self.alloc = [buf[f0 + q * fbytes: f0 + q * fbytes + nel * 8].view(torch.float64).view(self.lay.shape)
+                      for q in range(narr)]
+        arrs = [self.lay.view(a) for a in self.alloc]
+        self.f, self.aux = arrs[:2], arrs[2:]
+        # (world, K+1, slots, 2): slot 0 = the step kernels, slot 1 = the fix-up pass of a pair
         self.table = buf[_FLAG_BYTES: _FLAG_BYTES + self.world * (p.K + 1) * _SLOTS * 16].view(torch.float64).view(
             self.world, p.K + 1, _SLOTS, 2)
-        self.tab = [torch.from_numpy(t).to(self.device) for t in local_tables(p, blk)]
+        gd = 2 if self.pair else 1
+        self.tab_full = [torch.from_numpy(t).to(self.device) for t in local_tables(p, blk, ghosts=gd)]
+        self.tab = [t[gd - 1: t.numel() - (gd - 1)] for t in self.tab_full]
         self.status = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.ws = torch.zeros(cuda.workspace_bytes(), dtype=torch.uint8, device=self.device)
         self.trace = self.table[self.rank, :, 0]      # my row: the kernel writes it here and in every peer's copy
@@ -109,28 +130,30 @@ class FusedSolver:
                 r = blk.nbr[d][s]
                 if r < 0:
                     continue
-                pb = blocks[r]
-                pshape = cuda.field_shape(pb.n)
+                pb, pl = blocks[r], lay[r]
                 # my low edge fills the peer's HIGH ghost (index n+1), my high edge its LOW ghost (0)
                 ghost = pb.n[d] + 1 if s == 0 else 0
-                base = base_ptrs[r] if self.world > 1 else base_ptrs[0]
+                base = (base_ptrs[r] if self.world > 1 else base_ptrs[0]) + f0 + pl.origin
                 peers[d * 2 + s] = cuda.PeerSpec(
-                    field_ptrs=(base + f0, base + f0 + fbytes), ghost_index=ghost,
-                    pitch=pshape[2], plane=pshape[1] * pshape[2],
-                    flag_ptr=base + 8 * (d * 2 + (1 - s)))
-                peer_aux[d * 2 + s] = (base + f0 + 2 * fbytes, base + f0 + 3 * fbytes)
+                    field_ptrs=(base, base + fbytes), ghost_index=ghost, pitch=pl.pitch, plane=pl.plane,
+                    flag_ptr=(base_ptrs[r] if self.world > 1 else base_ptrs[0]) + 8 * (d * 2 + (1 - s)))
+                peer_aux[d * 2 + s] = (base + 2 * fbytes, base + 3 * fbytes)
         self.plan = cuda.CudaPlan(blk.n, self.f, self.tab, p.coeffs(), self.flags, self.status, self.ws,
                                   peers=peers, variant=variant, zchunk=zchunk, spin_timeout_ms=spin_timeout_ms,
                                   err_table_ptr=base_ptrs[self.rank if self.world > 1 else 0] + _FLAG_BYTES,
                                   err_table_peer_ptrs=[base_ptrs[r] + _FLAG_BYTES for r in range(self.world)
-                                                       if r != self.rank] if self.world > 1 else [])
+                                                       if r != self.rank] if self.world > 1 else [],
+                                  ghost_depth=gd)
         self.ct = time_table(p)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.kernel_launches = 0
-        # ---- temporal blocking (two steps per pass) ----
-        self.final_index = None          # array index (0..3) holding level K after run_steps in pair mode
+        # ---- time-level bookkeeping: which array holds the newest level and the one before ----
+        self.level, self._cur, self._prev = 0, 0, 1
+        self.final_index = None          # array index (0..3) holding the newest level after stepping in pair mode
+        self.pair_mode = cuda.PAIR_LOCAL
         if self.pair:
             self.plan.enable_pairs(self.aux[0], self.aux[1], pair_variant, zchunk, peer_aux)
+            self.pair_mode = self.plan.pair_mode
 
     # ------------------------------------------------------------------
     def describe(self) -> str:
@@ -148,48 +171,48 @@ class FusedSolver:
         into their ghosts, hence the barrier."""
         self.plan.init(zero_second=self._zero_second)
         self.table[self.rank].zero_()                    # only my own row: peers clear theirs
+        self.level, self._cur, self._prev = 0, 0, 1
+        self.final_index = 0
         self.barrier()
 
     def step(self, n: int, want_err: bool = True) -> None:
-        """Produce time level n (n = 1 is the Taylor step)."""
+        """Produce time level n (n = 1 is the Taylor step) with the one-pass-per-step kernel.
+
+        Works on whichever two arrays hold levels n-1 and n-2 (any of the four in pair mode)."""
         a, b, cs = step_coeffs(n)
         if n == 1 and not self._zero_second:
-            # init() skipped the zero fill of array 1 (even-K pair runs never read it); this
+            # init() skipped the zero fill of array 1 (pair runs never read it); this
             # single Taylor step does read it (times b = 0), so make sure it holds finite zeros
             self.f[1].zero_()
-        self.plan.step_fused(n - 1, a, b, cs, float(self.ct[n]), self.trace[n] if want_err else None)
+        err = self.trace[n] if want_err else None
+        if self.pair:
+            self.plan.step_fused_on(n - 1, self._cur, self._prev, a, b, cs, float(self.ct[n]), err)
+        else:
+            self.plan.step_fused(n - 1, a, b, cs, float(self.ct[n]), err)
         self.kernel_launches += 1
+        self._cur, self._prev = self._prev, self._cur
+        self.level = n
+        self.final_index = self._cur
 
     def _enqueue_steps(self, first: int, last: int) -> None:
-        if self.pair and first == 1:
-            self._enqueue_pairs(last)
+        """Levels first..last; level first-1 must be the newest one held."""
+        if self.pair:
+            n = first - 1
+            while n + 2 <= last:
+                n = self.pair_advance(n)
+            if n < last:                       # odd count: the last step goes alone, in place
+                self.step(last, last % self.every == 0)
             return
         for n in range(first, last + 1):
             self.step(n, n % self.every == 0)
 
-    def _enqueue_pairs(self, last: int) -> None:
-        """Levels 1..last with two steps per pass (plus one single step if `last` is odd).
+    def pair_advance(self, n: int, force_err: bool = False, before_fixup=None) -> int:
+        """Levels n+1 and n+2 from level n in ONE pass over memory; returns n + 2.
 
         Array roles rotate over the four arrays: (cur, prev) -> (out1, out2) = (0,1)->(2,3),
-        (3,2)->(0,1), (1,0)->(2,3), ...  With neighbours (or periodic axes) every pair is two
-        launches: the pair pass (which also ships the level-(n+1) faces) and the fix-up pass
-        that finishes level n+2 next to those faces and ships them."""
-        n = self.pair_begin(last)
-        while n < last:
-            n = self.pair_advance(n)
-
-    def pair_begin(self, last: int) -> int:
-        """Start a pair-mode run of `last` steps; returns the level reached (0, or 1 if odd)."""
-        self._cur, self._prev = 0, 1
-        n = 0
-        if last % 2 == 1:                 # odd count: the Taylor step goes alone, in place
-            self.step(1, 1 % self.every == 0)
-            n, self._cur, self._prev = 1, 1, 0
-        self.final_index = self._cur
-        return n
-
-    def pair_advance(self, n: int, force_err: bool = False) -> int:
-        """Levels n+1 and n+2 from level n; returns n + 2."""
+        (3,2)->(0,1), (1,0)->(2,3), ...  With neighbours (or periodic axes) the pass also does the
+        halo exchange: wide-halo protocol = this one launch; fix-up protocol (neighbours along
+        two or three axes) = a second launch that finishes level n+2 next to those faces."""
         cur, prev = self._cur, self._prev
         out1, out2 = (2, 3) if cur in (0, 1) else (0, 1)
         l1 = step_coeffs(n + 1) + (float(self.ct[n + 1]),)
@@ -199,10 +222,13 @@ class FusedSolver:
         self.plan.step_pair(n, cur, prev, out1, out2, l1, l2, self.trace[n + 1] if w1 else None,
                             self.trace[n + 2] if w2 else None)
         self.kernel_launches += 1
-        if any(r >= 0 for ax in self.blk.nbr for r in ax):
+        if self.pair_mode == cuda.PAIR_FIXUP:
+            if before_fixup is not None:           # test hook: e.g. a device-side delay between the two launches
+                before_fixup()
             self.plan.step_fixup(n + 1, out1, cur, out2, l2, self.trace_fix[n + 2] if w2 else None)
             self.kernel_launches += 1
         self._cur, self._prev = out2, out1
+        self.level = n + 2
         self.final_index = out2
         return n + 2
 
@@ -212,13 +238,14 @@ class FusedSolver:
             return
         # warm the kernels once outside capture (lazy module load is not capturable)
         self.init()
-        self._enqueue_steps(1, min(2, self.p.K))
+        self._enqueue_steps(1, min(3, self.p.K))
         self.barrier()
         g = torch.cuda.CUDAGraph()
         self.init()
         l0 = self.kernel_launches
         with torch.cuda.graph(g):
             self._enqueue_steps(1, self.p.K)
+        self._graph_state = (self.level, self._cur, self._prev, self.final_index)
         self._launches_per_run = self.kernel_launches - l0
         self.kernel_launches = l0
         self.graph = g
@@ -229,6 +256,7 @@ class FusedSolver:
         if self.use_graph and self.graph is not None:
             self.graph.replay()
             self.kernel_launches += self._launches_per_run
+            self.level, self._cur, self._prev, self.final_index = self._graph_state
         else:
             self._enqueue_steps(1, self.p.K)
 
@@ -254,6 +282,21 @@ class FusedSolver:
         return [(n, n * p.tau, float(mx[n]), math.sqrt(float(s2[n]) / p.n_unknowns))
                 for n in range(1, p.K + 1) if n % self.every == 0]
 
+    def exchange_stats(self) -> Dict[str, float]:
+        """Exchange time since the last init(), measured on the device and max-reduced over ranks.
+
+        ``flag_wait_s``: per launch, the longest any face CTA spun on its neighbours' flags;
+        ``halo_copy_s``: per launch, the longest halo copy-out (P2P stores + system fence); both
+        summed over the launches.  These are the counterparts of the reference's "MPI" and
+        "H2D/D2H" columns (report.pdf p.16 §4.4) — here they run underneath the interior CTAs."""
+        st = self.plan.exchange_stats()
+        if self.world > 1:
+            t = torch.tensor([st["flag_wait_s"], st["halo_copy_s"], st["max_flag_wait_s"], st["max_halo_copy_s"]],
+                             dtype=torch.float64, device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+            st["flag_wait_s"], st["halo_copy_s"], st["max_flag_wait_s"], st["max_halo_copy_s"] = (float(v) for v in t.cpu())
+        return st
+
     def run(self, verbose: bool = False) -> RunResult:
         """Whole run with device timing (CUDA events, max over ranks)."""
         p = self.p
@@ -264,6 +307,7 @@ class FusedSolver:
         ev[0].record()
         self.plan.init(zero_second=self._zero_second)
         self.table[self.rank].zero_()
+        self.level, self._cur, self._prev, self.final_index = 0, 0, 1, 0
         self.barrier()          # flags must be reset everywhere before anyone pushes
         ev[1].record()
         self.run_steps()
@@ -276,60 +320,84 @@ class FusedSolver:
         if self.world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX, group=self.group)
         t_init, t_loop = (float(v) for v in tt.cpu())
+        xs = self.exchange_stats()
         trace = self.gather_trace()
+        # `exchange` (flag waits + halo copy-out of the face CTAs) is measured inside the kernels and
+        # runs concurrently with the other CTAs: it is contained in `loop`, not added to it
         res = RunResult(backend="fused", N=p.N, L=p.L, tau=p.tau, K=p.K, bc=p.bc, world_size=self.world,
                         decomp=self.dims, trace=trace, updates=p.updates,
                         phases={"total": t_init + t_loop, "init": t_init, "compute": t_loop, "loop": t_loop,
-                                "h2d_d2h": 0.0, "exchange": 0.0},
-                        extra={"plan": self.describe(), "graph": bool(self.use_graph)})
+                                "h2d_d2h": 0.0, "exchange": xs["flag_wait_s"] + xs["halo_copy_s"],
+                                "flag_wait": xs["flag_wait_s"], "halo_copy": xs["halo_copy_s"]},
+                        extra={"plan": self.describe(), "graph": bool(self.use_graph), "exchange_stats": xs})
         if verbose and self.rank == 0:
             for line in res.lines(self.every):
                 print(line)
         return res
 
-    def field(self, parity: int) -> torch.Tensor:
+    def _owned(self, arr: torch.Tensor) -> torch.Tensor:
         xo = cuda.XOFF + 1
-        return self.f[parity][1:-1, 1:-1, xo: xo + self.blk.n[0]].contiguous()
+        return arr[1:-1, 1:-1, xo: xo + self.blk.n[0]].contiguous()
+
+    def field(self, parity: int) -> torch.Tensor:
+        return self._owned(self.f[parity])
 
     def final_field(self) -> torch.Tensor:
-        """Owned unknowns of the last level computed by run_steps (any mode)."""
+        """Owned unknowns of the newest level computed so far (any mode)."""
         if self.pair and self.final_index is not None:
-            arr = (self.f + self.aux)[self.final_index]
-            xo = cuda.XOFF + 1
-            return arr[1:-1, 1:-1, xo: xo + self.blk.n[0]].contiguous()
-        return self.field(self.p.K & 1)
+            return self._owned((self.f + self.aux)[self.final_index])
+        return self.field(self.level & 1)
 
     # -- tracing ---------------------------------------------------------------
     def profile_steps(self) -> List[float]:
-        """Device time of every step (ms, CUDA events, eager launches; max over ranks).
+        """Device time per step (ms, CUDA events, eager launches; max over ranks).
 
+        In pair mode two steps share a pass: each of them is reported with half the pass time.
         The per-step counterpart of the reference's summed phase timers (report.pdf
         p.16 §4.4); feed the result to ``utils.timing.write_chrome_trace``."""
         self.init()
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(self.p.K + 1)]
-        ev[0].record()
-        for n in range(1, self.p.K + 1):
-            self.step(n, n % self.every == 0)
-            ev[n].record()
+        K = self.p.K
+        marks = [(0, torch.cuda.Event(enable_timing=True))]
+        marks[0][1].record()
+        n = 0
+        while n < K:
+            if self.pair and n + 2 <= K:
+                n = self.pair_advance(n)
+            else:
+                n += 1
+                self.step(n, n % self.every == 0)
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            marks.append((n, e))
         self.barrier()
-        ms = torch.tensor([ev[n - 1].elapsed_time(ev[n]) for n in range(1, self.p.K + 1)],
-                          dtype=torch.float64, device=self.device)
+        ms = []
+        for (n0, e0), (n1, e1) in zip(marks[:-1], marks[1:]):
+            ms += [e0.elapsed_time(e1) / (n1 - n0)] * (n1 - n0)
+        t = torch.tensor(ms, dtype=torch.float64, device=self.device)
         if self.world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=self.group)
-        return [float(v) for v in ms.cpu()]
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return [float(v) for v in t.cpu()]
 
     # -- checkpoint / restart ----------------------------------------------------
     def run_range(self, first: int, last: int) -> None:
         """Eagerly run steps first..last (levels first-1 -> last)."""
+        if first - 1 != self.level:
+            raise ValueError(f"run_range({first}, {last}): the solver holds level {self.level}")
         self._enqueue_steps(first, last)
 
-    def save_checkpoint(self, path: str, level: int) -> str:
-        """Dump both local arrays (ghosts included) after time level ``level``."""
+    def save_checkpoint(self, path: str, level: Optional[int] = None) -> str:
+        """Dump the two live time levels (all ghost layers included) after the newest level.
+
+        In pair mode the live levels may sit in any two of the four arrays; the dump records
+        which, and a restart puts them back into the same arrays."""
         from ..utils import checkpoint
         self.barrier()
+        if level is not None and level != self.level:
+            raise ValueError(f"checkpoint asked for level {level} but the solver holds level {self.level}")
         meta = {"N": self.p.N, "L": self.p.L, "tau": self.p.tau, "K": self.p.K, "bc": self.p.bc,
-                "dims": self.dims, "rank": self.rank, "n": self.blk.n}
-        out = checkpoint.save_state(path, self.rank, level, self.f, meta)
+                "dims": self.dims, "rank": self.rank, "n": self.blk.n, "pair": self.pair,
+                "roles": (self._cur, self._prev), "shape": tuple(self.lay.shape)}
+        out = checkpoint.save_state(path, self.rank, self.level, [self.alloc[self._cur], self.alloc[self._prev]], meta)
         self.barrier()
         return out
 
@@ -339,12 +407,15 @@ class FusedSolver:
         st = checkpoint.load_state(path, self.rank)
         m = st["meta"]
         if tuple(m["N"]) != self.p.N or tuple(m["dims"]) != self.dims or m["bc"] != self.p.bc or \
-                tuple(m["n"]) != self.blk.n or abs(m["tau"] - self.p.tau) > 0:
-            raise ValueError(f"checkpoint {path} does not match this problem/decomposition: {m}")
+                tuple(m["n"]) != self.blk.n or abs(m["tau"] - self.p.tau) > 0 or \
+                bool(m.get("pair", False)) != self.pair or tuple(m.get("shape", self.lay.shape)) != tuple(self.lay.shape):
+            raise ValueError(f"checkpoint {path} does not match this problem/decomposition/mode: {m}")
         level = int(st["level"])
+        cur, prev = m.get("roles", (level & 1, (level & 1) ^ 1))
         self.plan.init()                       # clears status, counters
-        for dst, src in zip(self.f, st["fields"]):
-            dst.copy_(src)
+        self.alloc[cur].copy_(st["fields"][0])
+        self.alloc[prev].copy_(st["fields"][1])
+        self.level, self._cur, self._prev, self.final_index = level, cur, prev, cur
         # ghosts of `level` are part of the dump: tell the kernels they have arrived
         self.flags[:6].fill_(level)
         self.barrier()
@@ -382,31 +453,32 @@ class StreamingSession:
         """Upload the analytic tables from pinned host memory and build layer 0."""
         s = self.s
         from .decomp import local_tables
-        self.tab_host = [torch.from_numpy(t).pin_memory() for t in local_tables(s.p, s.blk)]
-        for dst, src in zip(s.tab, self.tab_host):
+        self.tab_host = [torch.from_numpy(t).pin_memory() for t in local_tables(s.p, s.blk, ghosts=2 if s.pair else 1)]
+        for dst, src in zip(s.tab_full, self.tab_host):
             dst.copy_(src, non_blocking=True)
         s.init()
 
     @property
     def table_bytes(self) -> int:
-        return sum(t.numel() * 8 for t in self.s.tab)
+        return sum(t.numel() * 8 for t in self.s.tab_full)
 
     def step_async(self, n: int) -> None:
         """Enqueue step n with its host input and the read-back of its result; do not wait.
 
         In pair mode two steps travel together: the call for the first step of a pair only
-        uploads its input, the call for the second one launches the pass and reads both back."""
+        uploads its input, the call for the second one launches the pass and reads both back;
+        the last step of an odd-length run goes alone."""
         s = self.s
         self.ct_dev[n: n + 1].copy_(self.ct_host[n: n + 1], non_blocking=True)
         if s.pair:
-            if n == 1:
-                self._level = s.pair_begin(s.p.K)       # runs step 1 alone when K is odd
-                if self._level == 1:
-                    self._finish(1, 1)
-                    return
-            if n == self._level + 2:
-                self._level = s.pair_advance(self._level, force_err=True)
+            if n == s.level + 2:
+                s.pair_advance(s.level, force_err=True)
                 self._finish(n - 1, n)
+            elif n == s.level + 1 and n == s.p.K:
+                s.step(n, True)
+                self._finish(n, n)
+            elif n != s.level + 1:
+                raise RuntimeError(f"step_async({n}): the solver holds level {s.level}; feed consecutive steps")
             return
         s.step(n, True)
         self._finish(n, n)

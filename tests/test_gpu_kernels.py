@@ -113,7 +113,7 @@ def test_step_vs_plain_pytorch_reference():
     s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
     res = s.run()
     ref_trace, ref_field = wave_torch.solve(p, every=1, return_field=True)
-    got = s.field(p.K & 1).cpu()
+    got = s.final_field().cpu()
     assert torch.max(torch.abs(got - ref_field[1:-1, 1:-1, 1:-1])) < 5e-15
     for a, b in zip(res.trace, ref_trace):
         assert abs(a[2] - b[2]) <= 5e-15 and abs(a[3] - b[3]) <= 1e-8 * b[3]
@@ -180,7 +180,7 @@ def test_fused_periodic_self_wrap_matches_cpu(bc):
     """Periodic axes on one GPU go through the same in-kernel peer-store + flag path."""
     from mpi_cuda_b200.parallel.fused import FusedSolver
     p = WaveProblem((40, 36, 28), 2.0, 1e-3, 8, bc=bc)
-    s = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=False)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=False, pair=False)
     res = s.run()
     base, _ = cpu.solve(p, every=2)
     for a, b in zip(res.trace, base):
@@ -190,11 +190,12 @@ def test_fused_periodic_self_wrap_matches_cpu(bc):
     assert np.array_equal(s.field(p.K & 1).cpu().numpy(), ref[p.K])
 
 
-def test_fused_graph_replay_equals_eager():
+@pytest.mark.parametrize("pair", [False, True])
+def test_fused_graph_replay_equals_eager(pair):
     from mpi_cuda_b200.parallel.fused import FusedSolver
     p = WaveProblem(64, 1.0, 1e-3, 10)
-    a = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=False).run()
-    g = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=True)
+    a = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=False, pair=pair).run()
+    g = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=True, pair=pair)
     r1 = g.run(); r2 = g.run()
     assert a.trace == r1.trace == r2.trace
     ora = analytic.oracle_trace(p, 2)
@@ -205,7 +206,7 @@ def test_fused_graph_replay_equals_eager():
 def test_streaming_session_matches_batch():
     from mpi_cuda_b200.parallel.fused import FusedSolver, StreamingSession
     p = WaveProblem(56, 1.0, 1e-3, 6)
-    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=False)
     batch = s.run().trace
     sess = StreamingSession(s)
     sess.start()
@@ -215,13 +216,17 @@ def test_streaming_session_matches_batch():
         assert mx == b[2] and abs(math.sqrt(s2 / p.n_unknowns) - b[3]) <= 1e-15 * b[3]
 
 
-def test_watchdog_trips_instead_of_hanging():
+@pytest.mark.parametrize("pair", [False, True])
+def test_watchdog_trips_instead_of_hanging(pair):
     """A halo flag that never arrives must end in an error code, not a hung GPU."""
     from mpi_cuda_b200.parallel.fused import FusedSolver
     p = WaveProblem(48, 2.0, 1e-3, 4, bc="ddp")
-    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, spin_timeout_ms=30)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, spin_timeout_ms=30, pair=pair)
     s.init()
-    s.step(2)                     # level 1 was never produced: its flag cannot arrive
+    if pair:
+        s.pair_advance(2)         # level 2 was never produced: its flag cannot arrive
+    else:
+        s.step(2)                 # level 1 was never produced: its flag cannot arrive
     torch.cuda.synchronize()
     with pytest.raises(RuntimeError, match="watchdog"):
         s.check_status()
@@ -229,25 +234,34 @@ def test_watchdog_trips_instead_of_hanging():
     s.check_status()
 
 
-def test_checkpoint_restart_is_bit_exact(tmp_path):
+@pytest.mark.parametrize("pair,at,bc", [(False, 6, "dpd"), (True, 6, "dpd"), (True, 5, "dpd"), (True, 4, "ppd")])
+def test_checkpoint_restart_is_bit_exact(tmp_path, pair, at, bc):
+    """Dump after level `at`, restore into a fresh solver, finish: same field and trace as one run.
+
+    Pair mode: the live levels sit in any two of the four arrays (the dump records which), an odd
+    `at` leaves the newest level produced by a single step, and "ppd" runs the fix-up protocol."""
     from mpi_cuda_b200.parallel.fused import FusedSolver
-    p = WaveProblem((60, 44, 36), 2.0, 1e-3, 10, bc="dpd")
-    a = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
+    p = WaveProblem((60, 44, 36), 2.0, 1e-3, 10, bc=bc)
+    a = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=pair)
     full = a.run().trace
-    want = a.field(p.K & 1).clone()
-    b = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
+    want = a.final_field().clone()
+    b = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=pair)
     b.init()
-    b.run_range(1, 6)
-    ck = b.save_checkpoint(str(tmp_path / "ck"), 6)
+    b.run_range(1, at)
+    ck = b.save_checkpoint(str(tmp_path / "ck"), at)
     assert ck.endswith(".rank0.pt")
-    c = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False)
+    c = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=pair)
     level = c.load_checkpoint(str(tmp_path / "ck"))
-    assert level == 6
+    assert level == at
     c.run_range(level + 1, p.K)
     c.barrier()
-    assert torch.equal(c.field(p.K & 1), want)
+    c.check_status()
+    assert torch.equal(c.final_field(), want)
     got = c.gather_trace()
-    assert got[6:] == full[6:]
+    # (an odd `at` moves the lone single step from the end of the run to the middle: the max is
+    # digit-identical, the sum of squares is folded in a different order)
+    for x, y in zip(got[at:], full[at:]):
+        assert x[0] == y[0] and x[2] == y[2] and abs(x[3] - y[3]) <= 1e-12 * y[3]
 
 
 def test_profile_steps_and_chrome_trace(tmp_path):
@@ -283,7 +297,7 @@ def test_golden_trace_512_on_gpu():
     """Published trace of the reference (report.pdf p.15-16 §4.3), on one B200."""
     from mpi_cuda_b200.parallel.fused import FusedSolver
     p = WaveProblem(512, 1.0, 1e-3, 20)
-    s = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=True)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=True, pair=False)
     res = s.run()
     assert len(res.trace) == 10
     for (n, t, mx, l2), (gn, gt, gmx, gl2) in zip(res.trace, report.GOLDEN_512):
@@ -313,7 +327,7 @@ def test_native_mpigpu_executable_matches_python_path():
     assert len(got) == 5 and abs(got[-1][2] - base[-1][2]) <= 1e-6 * base[-1][2]
 
 
-@pytest.mark.parametrize("pair_variant", [0, 1, 2, 3, 4, 5, 6, 7])
+@pytest.mark.parametrize("pair_variant", [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10])
 @pytest.mark.parametrize("N,K", [((70, 45, 37), 6), ((130, 66, 50), 7), ((257, 40, 23), 4)])
 def test_pair_kernel_bit_exact_vs_cpu(N, K, pair_variant):
     """Temporal blocking (two steps per pass) must give exactly the fields of K single steps."""
@@ -330,13 +344,18 @@ def test_pair_kernel_bit_exact_vs_cpu(N, K, pair_variant):
         assert a[2] == c[2] and abs(a[3] - c[3]) <= 1e-12 * c[3]
 
 
-@pytest.mark.parametrize("bc", ["ddp", "dpd", "pdd", "ppp"])
+@pytest.mark.parametrize("bc", ["ddp", "dpd", "pdd", "ppp", "dpp"])
 @pytest.mark.parametrize("K", [6, 7])
 def test_pair_mode_with_periodic_faces_matches_cpu(bc, K):
-    """Two-step passes + fix-up pass with in-kernel halo exchange (periodic axes wrap onto the GPU)."""
+    """Two-step passes with in-kernel halo exchange (periodic axes wrap onto the GPU itself).
+
+    One periodic axis: wide halo (one launch, one handshake per two steps); two or three:
+    the fix-up protocol."""
+    from mpi_cuda_b200.ops import cuda
     from mpi_cuda_b200.parallel.fused import FusedSolver
     p = WaveProblem((70, 45, 37), 2.0, 1e-3, K, bc=bc)
     s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=True)
+    assert s.pair_mode == (cuda.PAIR_WIDE if bc.count("p") == 1 else cuda.PAIR_FIXUP)
     res = s.run()
     s.check_status()
     ref, _, _ = _cpu_fields(p, K)
@@ -373,3 +392,56 @@ def test_small_and_odd_blocks(N, K, bc, pair):
     base, _ = cpu.solve(p, every=1)
     for a, c in zip(res.trace, base):
         assert a[2] == c[2] and abs(a[3] - c[3]) <= 1e-12 * max(c[3], 1e-300)
+
+
+@pytest.mark.parametrize("N,bc,zchunk,pv", [((65, 40, 30), "pdd", 0, -1), ((40, 33, 30), "dpd", 0, -1),
+                                            ((70, 66, 65), "ddp", 64, -1), ((129, 30, 33), "pdd", 16, 9),
+                                            ((48, 61, 40), "dpd", 7, 8), ((30, 30, 3), "ddp", 0, -1),
+                                            ((3, 40, 20), "pdd", 0, -1), ((40, 3, 20), "dpd", 1, -1)])
+@pytest.mark.parametrize("K", [4, 5])
+def test_wide_halo_edge_geometries(N, bc, zchunk, pv, K):
+    """Wide-halo pair passes where the shipped layers straddle tiles / chunks.
+
+    A periodic axis with n = 1 (mod tile) puts the ghost column inside a partial tile and the
+    layers n-1, n into different tiles; zchunk leaves thin last chunks; 2- and 3-node-thick
+    blocks make the two shipped layers of both faces overlap.  Bit-exact against the CPU."""
+    from mpi_cuda_b200.ops import cuda
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem(N, 3.0, 1e-3, K, bc=bc)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=True, zchunk=zchunk, pair_variant=pv)
+    assert s.pair_mode == cuda.PAIR_WIDE
+    res = s.run()
+    s.check_status()
+    ref, _, _ = _cpu_fields(p, K)
+    got = s.final_field().cpu().numpy()
+    assert np.array_equal(got, ref[K]), f"max diff {np.max(np.abs(got - ref[K]))}"
+    base, _ = cpu.solve(p, every=1)
+    for a, c in zip(res.trace, base):
+        assert a[2] == c[2] and abs(a[3] - c[3]) <= 1e-12 * max(c[3], 1e-300)
+    assert s.run().trace == res.trace          # second run on the same arrays (stale ghosts must not matter)
+
+
+def test_exchange_statistics_are_measured():
+    """The phase table's exchange columns come from %globaltimer stamps inside the face CTAs."""
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem((128, 128, 64), 2.0, 1e-3, 8, bc="ddp")
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=True, pair=True)
+    r = s.run()
+    xs = r.extra["exchange_stats"]
+    assert xs["launches"] == 4                      # one handshake per two steps
+    assert 0 < r.phases["halo_copy"] < r.phases["loop"] and r.phases["flag_wait"] >= 0
+    assert r.phases["exchange"] == r.phases["flag_wait"] + r.phases["halo_copy"]
+    f = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=False, pair=False)
+    assert f.run().extra["exchange_stats"]["launches"] == 8
+
+
+@pytest.mark.parametrize("N,L,want", [(512, math.pi, 6.141989e-10), (128, math.pi, 1.071891e-08)])
+def test_published_delta_on_L_pi(N, L, want):
+    """delta for Omega = [0,pi]^3 as published (report.pdf p.8, p.10, p.11: 1.07e-8 / 6.14e-10)."""
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem(N, L, 1e-3, 20)
+    res = FusedSolver(p, (1, 1, 1), _dev(), every=2, use_graph=True).run()
+    n, t, mx, l2 = res.trace[-1]
+    assert n == 20 and abs(l2 - want) <= 2e-6 * want
+    omx, ol2 = analytic.oracle_errors(p, 20)
+    assert abs(mx - omx) <= 5e-15 and abs(l2 - ol2) <= 1e-6 * ol2
