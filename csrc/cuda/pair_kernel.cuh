@@ -39,6 +39,10 @@
 #pragma once
 #include "kernels.cuh"
 
+#ifndef W3D_PAIR_THREAD_DISPATCH
+#define W3D_PAIR_THREAD_DISPATCH 0
+#endif
+
 namespace w3d {
 
 template <int TX, int RPT, int RG, int STAGES, int MINB = 1>
@@ -95,6 +99,9 @@ struct alignas(64) PairParams {
   unsigned* shell_counter;
   unsigned* status;
   XStat* xstat;
+  int seq;                  // launch sequence number of this plan (parity selects the XStat slot)
+  int defer_release;        // wide halo: level `level` is published at kernel entry (entry_release, kernels.cuh)
+  unsigned long long* tl;   // timeline slot of this launch: [0] earliest CTA start, [1] latest CTA end (or null)
   unsigned long long level;
   unsigned long long release;
   unsigned long long timeout_ns;
@@ -107,6 +114,11 @@ struct alignas(64) PairParams {
   // where that face has a neighbour; 1 .. n otherwise), and is stored on the ghost layer too
   int in_lo[3], in_hi[3];
   int wide;
+  // wide halo, z faces: the shipped planes of level n+2 go to the neighbour straight from the
+  // registers that hold them when they are stored locally (bit 0: low face, bit 1: high face), so
+  // nothing but the fence and the flag release is left for the end of the pass.  x / y faces
+  // (strided) are copied out after the loop by face_copy_out.
+  int zpush;
 };
 
 // Consumer side of one CTA.  FULL = every node of the tile is inside the block, is
@@ -130,7 +142,7 @@ __device__ __forceinline__ void pair_issue(const PairParams& P, uint64_t* full, 
 
 template <class Cfg, bool FULL, bool XFULL>
 __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* full, uint8_t* stage0,
-                                              double* l1buf, const double* s_sz, int x0, int y0, int z0, int z1,
+                                              double* l1buf, const double* s_sz, int x0, int y0, int yown, int z0, int z1,
                                               double& mx1, double& s21, double& mx2, double& s22) {
   constexpr int TX = Cfg::kTX, RPT = Cfg::kRPT, STAGES = Cfg::kStages;
   constexpr int WA = Cfg::kWA, WB = Cfg::kWB, W1 = Cfg::kW1;
@@ -148,7 +160,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
   const double ct1 = P.ct_ptr ? __ldg(P.ct_ptr) : P.ct1, ct2 = P.ct_ptr ? __ldg(P.ct_ptr + 1) : P.ct2;
   double acc1[RPT], zA[RPT], acc2[RPT], zL[RPT], sxy[RPT];
   double zA1[RPT], zL1[RPT];            // second register set of the z pipeline (see `iter`)
-  bool in1[RPT], st1[RPT], st2[RPT], own[RPT];
+  bool in1[RPT], st1[RPT], st2[RPT], own[RPT], ec1[RPT], ec2[RPT];
   const double sxv = x_in ? P.sx[gx] : 0.0;
 #pragma unroll
   for (int r = 0; r < RPT; ++r) {
@@ -166,6 +178,10 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
     st1[r] = own[r] || (!(FULL && XFULL) && P.wide && in1[r] && ((xg && y_ok) || (yg && x_ok)));
     st2[r] = own[r] && (XFULL || (!(P.skip_lo[0] && gx == 1) && !(P.skip_hi[0] && gx == g.n[0]))) &&
              (FULL || (!(P.skip_lo[1] && gy == 1) && !(P.skip_hi[1] && gy == g.n[1])));
+    // rows below yown belong to the previous tile row as well (a last tile row that was moved back so that
+    // it is complete): both tiles compute and store them, identically; only one may count their error
+    ec1[r] = own[r] && gy >= yown;
+    ec2[r] = st2[r] && gy >= yown;
     sxy[r] = in1[r] ? sxv * P.sy[min(max(gy, 0), g.n[1] + 1)] : 0.0;
     acc1[r] = zA[r] = acc2[r] = zL[r] = zA1[r] = zL1[r] = 0.0;
   }
@@ -200,26 +216,45 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
   const int off1 = (r0 + 1) * W1 + cxi + 1;      // level-1 plane: tile node (cxi, r0)
   const int offRA = (rry + 1) * WA + rcx + 1, offRB = rry * WB + rcx + 1, offR1 = rry * W1 + rcx;
 
-  // One plane.  zAp/zLp hold u^n / level 1 of the previous plane (own column), zAc/zLc receive
-  // those of the current plane; the caller alternates the two register sets, so the z pipeline
-  // advances without any register-to-register copies.
-  auto iter = [&](const int t, double (&zAp)[RPT], double (&zLp)[RPT], double (&zAc)[RPT], double (&zLc)[RPT]) {
+  // wide halo, z faces pushed from the loop: per-thread base pointers into the neighbours' arrays
+  // (ghost plane index is added per plane), null when that face is not pushed
+  const PeerDev& pzl = P.peer[4];
+  const PeerDev& pzh = P.peer[5];
+  double* const zpl = (P.zpush & 1) ? pzl.field + (long long)(y0 + r0) * pzl.pitch + g.xoff + gx : nullptr;
+  double* const zph = (P.zpush & 2) ? pzh.field + (long long)(y0 + r0) * pzh.pitch + g.xoff + gx : nullptr;
+  const int nzl = g.n[2];
+  // z table entries for the error epilogues, loaded one plane ahead: szc = s_sz[t-1] (level-1 plane
+  // finished in l1_phase(t)), szo = s_sz[t-2] (level-2 plane finished in l2_phase(t)).  A load at the
+  // point of use exposed the shared-memory latency to every warp once per plane and level.
+  double szc = 0.0, szo = 0.0, szn = 0.0;
+
+  // The z pipeline of one plane is split in two phases.  zAp/zLp hold u^n / level 1 of the previous
+  // plane (own column), zAc/zLc receive those of the current plane; the caller alternates the two
+  // register sets, so the pipeline advances without any register-to-register copies.
+  //
+  // l1_phase(t): plane p = z0-2+t of u^n has arrived -> level 1 of plane p-1 is finished (shared
+  // memory, global, error) and the partial sums of plane p are formed.
+  //
+  // S ("steady", always a literal at the call sites, so it folds after inlining) marks the planes in the middle of the chunk, t in [6, nzc+2):
+  // every CTA-uniform condition of the general code is known there (the level-1 plane is owned and
+  // stored, level 2 is owned, no ghost plane, no shipped plane, no skipped plane), so the body has
+  // no uniform compare-and-branch chains (ncu: 35 of 332 instructions per warp and plane) and the
+  // scheduler sees one large basic block per phase.
+  auto l1_phase = [&](const bool S, const int t, double (&zAp)[RPT], double (&zAc)[RPT], double (&zLc)[RPT]) {
     const int s = t % STAGES;
-    const uint32_t ph = (uint32_t)(t / STAGES) & 1u;
     const int p = z0 - 2 + t;                 // plane of u^n that has just arrived
-    mbar_wait(full + s, ph);
     const double* As = reinterpret_cast<const double*>(stage0 + (size_t)s * Cfg::kStageBytes);
     const double* Bs = reinterpret_cast<const double*>(stage0 + (size_t)s * Cfg::kStageBytes + Cfg::kABytes);
     double* L1w = l1buf + (size_t)((t + 1) & 1) * (Cfg::kL1Bytes / 8);     // plane p-1 of level 1
-    // ---- level 1 ----
+    szn = s_sz[t];                                        // used one plane later
     const double aTop = As[offA];                         // row above this thread's rows
     const double aBot = As[offA + (RPT + 1) * WA];        // row below
 #pragma unroll
     for (int r = 0; r < RPT; ++r) zAc[r] = As[offA + (r + 1) * WA];
     const int p1 = p - 1;                                        // level-1 plane completed now
-    const bool p1_live = t >= 2 && p1 >= zl1_lo && p1 <= zl1_hi;  // otherwise level 1 is 0 there
-    const bool p1_store = p1 >= z0 && p1 < z1;
-    const bool p_l1 = p >= z0 - 1 && p <= z1;                   // plane p needs a level-1 partial
+    const bool p1_live = S || (t >= 2 && p1 >= zl1_lo && p1 <= zl1_hi);  // otherwise level 1 is 0 there
+    const bool p1_store = S || (p1 >= z0 && p1 < z1);
+    const bool p_l1 = S || (p >= z0 - 1 && p <= z1);                   // plane p needs a level-1 partial
 #pragma unroll
     for (int r = 0; r < RPT; ++r) zLc[r] = w3d_finish(acc1[r], zAc[r], P.c1z);
     if (!p1_live) {
@@ -231,7 +266,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
     }
 #pragma unroll
     for (int r = 0; r < RPT; ++r) L1w[off1 + r * W1] = zLc[r];
-    if (p1 == zg_lo || p1 == zg_hi) {
+    if (!S && (p1 == zg_lo || p1 == zg_hi)) {
       // wide halo: level 1 on the first ghost plane, kept as the next pass's u^{n-1} halo
       double* o = o1 + (long long)p1 * g.plane;
 #pragma unroll
@@ -244,10 +279,10 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
       for (int r = 0; r < RPT; ++r)
         if (st1[r]) o[r * pitch] = zLc[r];
       if (want1) {
-        const double szt = s_sz[t - 1] * ct1;      // s_sz[i] = sz[z0 - 2 + i]
+        const double szt = szc * ct1;              // szc = s_sz[t - 1]; s_sz[i] = sz[z0 - 2 + i]
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
-          if (own[r]) {
+          if (ec1[r]) {
             const double e = w3d_abs_err(zLc[r], sxy[r], szt);
             mx1 = fmax(mx1, e);
             s21 = fma(e, e, s21);
@@ -279,12 +314,16 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
       }
     }
     rzA = ring_c;
-    __syncthreads();          // level-1 plane p-1 is complete in smem AND every thread is done with stage s
-    if (tid == 0 && t + STAGES < iters) pair_issue<Cfg>(P, full, stage0, t + STAGES, x0, y0, z0, nzc);
-    // ---- level 2 ----
-    const int p2 = p - 2;                                        // level-2 plane completed now
-    if (p2 >= z0 && p2 < z1) {
-      const bool skipz = (P.skip_lo[2] && p2 == 1) || (P.skip_hi[2] && p2 == g.n[2]);
+  };
+  // l2_phase(t): the level-1 plane p-1 is complete in shared memory (CTA barrier) -> level 2 of
+  // plane p-2 is finished (global, pushed to a z neighbour when it is one of the two outermost
+  // planes, error) and the partial sums of plane p-1 are formed.
+  auto l2_phase = [&](const bool S, const int t, double (&zAp)[RPT], double (&zLp)[RPT], double (&zLc)[RPT]) {
+    const int p = z0 - 2 + t;
+    const double* L1w = l1buf + (size_t)((t + 1) & 1) * (Cfg::kL1Bytes / 8);
+    const int p1 = p - 1, p2 = p - 2;                              // level-2 plane completed now: p2
+    if (S || (p2 >= z0 && p2 < z1)) {
+      const bool skipz = !S && ((P.skip_lo[2] && p2 == 1) || (P.skip_hi[2] && p2 == g.n[2]));
       double v2[RPT];
 #pragma unroll
       for (int r = 0; r < RPT; ++r) v2[r] = w3d_finish(acc2[r], zLc[r], P.c2z);
@@ -293,11 +332,25 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
 #pragma unroll
         for (int r = 0; r < RPT; ++r)
           if (st2[r]) o[r * pitch] = v2[r];
+        if (!S && zpl != nullptr && p2 <= 2) {            // my planes 1, 2 -> the low neighbour's ghost planes n'+1, n'+2
+          double* q = zpl + (long long)(pzl.ghost_index + (p2 - 1)) * pzl.plane;
+          const int pp = (int)pzl.pitch;
+#pragma unroll
+          for (int r = 0; r < RPT; ++r)
+            if (st2[r]) q[r * pp] = v2[r];
+        }
+        if (!S && zph != nullptr && p2 >= nzl - 1) {      // my planes n-1, n -> the high neighbour's ghost planes -1, 0
+          double* q = zph + (long long)(pzh.ghost_index - (nzl - p2)) * pzh.plane;
+          const int pp = (int)pzh.pitch;
+#pragma unroll
+          for (int r = 0; r < RPT; ++r)
+            if (st2[r]) q[r * pp] = v2[r];
+        }
         if (want2) {
-          const double szt = s_sz[t - 2] * ct2;
+          const double szt = szo * ct2;              // szo = s_sz[t - 2]
 #pragma unroll
           for (int r = 0; r < RPT; ++r) {
-            if (st2[r]) {
+            if (ec2[r]) {
               const double e = w3d_abs_err(v2[r], sxy[r], szt);
               mx2 = fmax(mx2, e);
               s22 = fma(e, e, s22);
@@ -306,7 +359,7 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
         }
       }
     }
-    if (p1_store) {
+    if (S || (p1 >= z0 && p1 < z1)) {
       const double ym0 = L1w[off1 - W1];                 // row above this thread's rows
       const double ypN = L1w[off1 + RPT * W1];           // row below
 #pragma unroll
@@ -318,10 +371,42 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
         acc2[r] = w3d_partial(zLc[r], zAp[r], xm, xp, ym, yp, zLp[r], P.a2, P.b2, P.c2x, P.c2y, P.c2z);
       }
     }
+    szo = szc;
+    szc = szn;
   };
-  for (int t = 0; t < iters; t += 2) {
-    iter(t, zA, zL, zA1, zL1);
-    if (t + 1 < iters) iter(t + 1, zA1, zL1, zA, zL);
+  auto wait_stage = [&](const int t) { mbar_wait(full + t % STAGES, (uint32_t)(t / STAGES) & 1u); };
+  auto sync_and_refill = [&](const int t) {
+    __syncthreads();          // level-1 plane p-1 is complete in smem AND every thread is done with stage t % STAGES
+    if (tid == 0 && t + STAGES < iters) pair_issue<Cfg>(P, full, stage0, t + STAGES, x0, y0, z0, nzc);
+  };
+  // General plane (any special case; a few planes at both ends of the chunk): ONE copy of the code, the
+  // z pipeline registers are moved by hand.  Steady planes: two per call with the register sets
+  // alternating.  Keeping the general code to a single call site matters: with head / steady / tail
+  // each inlined twice the kernel grew from 6.8 k to 14.4 k instructions and ran up to 50 % slower.
+  auto one_plane = [&](const int t) {
+    wait_stage(t);
+    l1_phase(false, t, zA, zA1, zL1);
+    sync_and_refill(t);
+    l2_phase(false, t, zA, zL, zL1);
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) { zA[r] = zA1[r]; zL[r] = zL1[r]; }
+  };
+  auto two_steady_planes = [&](const int t) {
+    wait_stage(t);
+    l1_phase(true, t, zA, zA1, zL1);
+    sync_and_refill(t);
+    l2_phase(true, t, zA, zL, zL1);
+    wait_stage(t + 1);
+    l1_phase(true, t + 1, zA1, zA, zL);
+    sync_and_refill(t + 1);
+    l2_phase(true, t + 1, zA1, zL1, zL);
+  };
+  constexpr int kHead = 6;                                          // planes with special cases at the chunk's start
+  const int t_steady_end = kHead + (max(nzc + 2 - kHead, 0) & ~1);  // steady planes: [kHead, nzc+2), whole pairs
+#pragma unroll 1
+  for (int t = 0; t < iters;) {
+    if (t >= kHead && t < t_steady_end) { two_steady_planes(t); t += 2; }
+    else { one_plane(t); ++t; }
   }
 }
 
@@ -344,13 +429,19 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
   const int ty = (work / T.ntx) % T.nty;
   const int ch = work / (T.ntx * T.nty);
   const int x0 = T.x0 + tx * TX;
-  const int y0 = T.lo[1] + ty * Cfg::kTY;
+  // A last tile row that would be partial is moved back so that it ends exactly at the block's last row: it
+  // overlaps the previous tile row in rows [y0, yown), which both compute and store identically (inputs and
+  // outputs are different arrays), and every tile runs the predicate-free code.  In a one-wave launch the
+  // slowest CTA sets the pass time, and the partial tiles were that CTA (mirrored in pair_tile_y0(), wave_api.cu).
+  const int yown = T.lo[1] + ty * Cfg::kTY;
+  const int y0 = (yown + Cfg::kTY > T.hi[1] && T.hi[1] - Cfg::kTY >= T.lo[1]) ? T.hi[1] - Cfg::kTY : yown;
   const int z0 = T.lo[2] + ch * T.zc;
   const int z1 = min(z0 + T.zc, T.hi[2]);
   const int nzc = z1 - z0;
   const int iters = nzc + 4;          // planes z0-2 .. z1+1 of u^n
 
   double mx1 = 0.0, s21 = 0.0, mx2 = 0.0, s22 = 0.0;
+  if (P.tl && threadIdx.x == 0) atomicMin(P.tl, globaltimer_ns());
   // copy-out mask: faces of which this tile owns one of the halo_depth outermost layers; wait
   // mask: faces whose ghost layers it reads — the level-1 ring reaches one node further than the
   // tile, so a tile that ends one layer short of a face (hi == n, lo == 2) reads that ghost too
@@ -358,11 +449,22 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
   const int mask = tile_face_mask(P, x0, y0, z0, z1, TX, Cfg::kTY, P.halo_depth);
   const int wmask = tile_face_mask(P, x0, y0, z0, z1, TX, Cfg::kTY, 2);
   unsigned long long wait_ns = 0ull;
+  // wide halo: tell the neighbours that the layers pushed by the previous launch have landed (first thing, it
+  // is on their critical path)
+  if (P.defer_release && P.use_flags && blockIdx.x == 0 && threadIdx.x == 0) entry_release(P);
+  // z slice of the analytic table for the error epilogue (a global load per plane inside the
+  // loop exposed its full latency to every warp: ncu, top long-scoreboard stall)
+  for (int i = threadIdx.x; i < iters && i < Cfg::kSzEntries; i += Cfg::kThreads) {
+    const int k = z0 - 2 + i;
+    s_sz[i] = (k >= 0 && k <= g.n[2] + 1) ? P.sz[k] : 0.0;
+  }
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
     fence_barrier_init();
     tma_prefetch_desc(&P.map_a);
     tma_prefetch_desc(&P.map_b);
+  }
+  if (threadIdx.x == 0) {
     if (wmask) wait_ns = wait_peer_flags(P, wmask);    // ghosts of u^n must have arrived before they are loaded
     for (int t = 0; t < STAGES && t < iters; ++t) pair_issue<Cfg>(P, full, stage0, t, x0, y0, z0, nzc);
   }
@@ -374,41 +476,51 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
       for (int i = threadIdx.x; i < Cfg::kBBytes / 8; i += Cfg::kThreads) bs[i] = 0.0;
     }
   }
-  // z slice of the analytic table for the error epilogue (a global load per plane inside the
-  // loop exposed its full latency to every warp: ncu, top long-scoreboard stall)
-  for (int i = threadIdx.x; i < iters && i < Cfg::kSzEntries; i += Cfg::kThreads) {
-    const int k = z0 - 2 + i;
-    s_sz[i] = (k >= 0 && k <= g.n[2] + 1) ? P.sz[k] : 0.0;
-  }
   __syncthreads();
   {
-    // FULL: tile complete in y and free of skipped rows; XFULL: the same in x
-    const bool full_tile = y0 + Cfg::kTY <= T.hi[1] && !(P.skip_lo[1] && y0 <= 1) &&
-                           !(P.skip_hi[1] && y0 + Cfg::kTY > g.n[1]);
+    // Fast paths are chosen per THREAD GROUP (the TX threads that share a set of rows = whole warps):
+    // FULL: all rows of this thread are owned, updated and free of skipped rows; XFULL: the tile is
+    // complete in x and free of skipped columns.  In a tile that is only partial in y just the
+    // row group that holds the dead rows pays for predicates — in a one-wave launch the slowest
+    // CTA sets the pass time, and before this split every CTA of the last tile row was that CTA.
+    // (All instantiations have the same barrier structure: one CTA barrier per plane.)
+#if W3D_PAIR_THREAD_DISPATCH
+    const int gy0 = y0 + (threadIdx.x / TX) * Cfg::kRPT, gy1 = gy0 + Cfg::kRPT;
+#else
+    const int gy0 = y0, gy1 = y0 + Cfg::kTY;       // whole tile: one code path per CTA
+#endif
+    const bool rows_full = gy0 >= T.lo[1] && gy1 <= T.hi[1] && !(P.skip_lo[1] && gy0 <= 1) &&
+                           !(P.skip_hi[1] && gy1 > g.n[1]);
     const bool xfull = x0 >= T.lo[0] && x0 >= 1 && x0 + TX <= T.hi[0] && !(P.skip_lo[0] && x0 <= 1) &&
                        !(P.skip_hi[0] && x0 + TX > g.n[0]);
-    if (full_tile && xfull)
-      pair_consumer<Cfg, true, true>(P, full, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
-    else if (full_tile)
-      pair_consumer<Cfg, true, false>(P, full, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
+    if (rows_full && xfull)
+      pair_consumer<Cfg, true, true>(P, full, stage0, l1buf, s_sz, x0, y0, yown, z0, z1, mx1, s21, mx2, s22);
+    else if (rows_full)
+      pair_consumer<Cfg, true, false>(P, full, stage0, l1buf, s_sz, x0, y0, yown, z0, z1, mx1, s21, mx2, s22);
     else
-      pair_consumer<Cfg, false, false>(P, full, stage0, l1buf, s_sz, x0, y0, z0, z1, mx1, s21, mx2, s22);
+      pair_consumer<Cfg, false, false>(P, full, stage0, l1buf, s_sz, x0, y0, yown, z0, z1, mx1, s21, mx2, s22);
     if (mask) {
-      __syncthreads();   // the tile's shipped level is written (CTA-visible)
+      __syncthreads();   // the tile's shipped level is written (CTA-visible), z-face pushes are issued
       const unsigned long long t_copy0 = P.xstat ? globaltimer_ns() : 0ull;
-      face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kThreads);
-      __syncthreads();
-      if (threadIdx.x == 0) face_cta_done(P, wait_ns, t_copy0);
+      const int cmask = mask & ~((P.zpush & 1 ? 16 : 0) | (P.zpush & 2 ? 32 : 0));   // faces still to copy: x, y
+      if (cmask) {
+        face_copy_out(P, cmask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kThreads);
+        __syncthreads();
+      }
+      if (threadIdx.x == 0) {
+        if (!P.defer_release) face_cta_done(P, wait_ns, t_copy0);
+        else if (P.xstat) {             // kernel completion delivers the halos; the next launch publishes them
+          atomicMax(&P.xstat->cur_wait[P.seq & 1], wait_ns);
+          atomicMax(&P.xstat->cur_copy[P.seq & 1], globaltimer_ns() - t_copy0);
+        }
+      }
     }
   }
-  if (P.err1.out != nullptr) {
+  if (P.err1.out != nullptr || P.err2.out != nullptr) {
     __syncthreads();
-    publish_error(P.err1, mx1, s21, red);
+    publish_error2(P.err1, P.err2, mx1, s21, mx2, s22, red, reinterpret_cast<int*>(smem + 96));
   }
-  if (P.err2.out != nullptr) {
-    __syncthreads();
-    publish_error(P.err2, mx2, s22, red);
-  }
+  if (P.tl && threadIdx.x == 0) atomicMax(P.tl + 1, globaltimer_ns());
 }
 
 }  // namespace w3d

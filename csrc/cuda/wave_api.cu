@@ -74,6 +74,8 @@ using PCfg7 = PairCfg<64, 4, 4, 4, 2>; // same with a 4-stage ring (~108 KB)
 using PCfg8 = PairCfg<64, 5, 6, 3>;    // 384 threads, 5 rows per thread
 using PCfg9 = PairCfg<64, 3, 10, 3>;   // 640 threads, 3 rows per thread
 using PCfg10 = PairCfg<64, 6, 5, 4>;   // 320 threads, 6 rows per thread, 4-stage ring
+// (tried and dropped: 128 x 14 / 128 x 15 tiles — 4 x 37 = 148 / 4 x 35 = 140 CTAs at 511 x 511 — with 2 / 3
+// rows per thread: 0.085 / 0.072 ms per step on the 511 x 511 x 64 block against 0.057 for 64 x 32)
 struct PairVariant {
   int tx, ty, threads, smem, ctas_per_sm;
   void (*kernel)(const PairParams);
@@ -147,6 +149,9 @@ struct W3dPlan {
   bool pair_ready;
   int pair_mode;                   // W3D_PAIR_LOCAL / WIDE / FIXUP
   int step_depth;                  // halo layers the single-step kernel ships: 1, or 2 in wide-halo plans
+  int launch_seq;                  // launches issued through this plan (parity selects the XStat slot)
+  unsigned long long* timeline;    // optional device buffer of (start, end) stamps per launch, indexed by level
+  int timeline_cap;
   long long launches;
   char text[1024];
 };
@@ -231,6 +236,13 @@ void plan_tiles(const W3dPlan* p, const int lo[3], const int hi[3], int zchunk, 
   t->nchunks = (ez + t->zc - 1) / t->zc;
 }
 
+// first row of tile row `ty` of the pair kernel: a last tile row that would be partial is moved back so that
+// it is complete (mirror of the y0 computation in pair_step_kernel)
+int pair_tile_y0(const TileGeom& t, int ty, int tile_y) {
+  const int y = t.lo[1] + ty * tile_y;
+  return (y + tile_y > t.hi[1] && t.hi[1] - tile_y >= t.lo[1]) ? t.hi[1] - tile_y : y;
+}
+
 // host mirror of tile_face_mask() (kernels.cuh)
 int face_mask_host(const W3dPlanDesc& d, const int n[3], const int lo[3], const int hi[3], int reach) {
   int m = 0;
@@ -297,6 +309,9 @@ void fill_common(const W3dPlan* p, StepParams* P, int s, double a, double b, dou
   P->level = (unsigned long long)s;
   P->release = (unsigned long long)s + 1ull;
   P->halo_depth = p->step_depth;
+  P->seq = const_cast<W3dPlan*>(p)->launch_seq++;
+  P->defer_release = p->pair_mode == W3D_PAIR_WIDE ? 1 : 0;
+  P->tl = (p->timeline && s >= 0 && s < p->timeline_cap) ? p->timeline + 2 * (size_t)s : nullptr;
   P->xstat = reinterpret_cast<XStat*>(static_cast<char*>(p->d.workspace) + kXStatOffset);
   P->timeout_ns = (unsigned long long)(p->d.spin_timeout_ms > 0 ? p->d.spin_timeout_ms : 10000) * 1000000ull;
 }
@@ -358,6 +373,9 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
   }
   p->pair_mode = W3D_PAIR_LOCAL;
   p->step_depth = 1;
+  p->timeline = nullptr;
+  p->timeline_cap = 0;
+  p->launch_seq = 0;
   p->variant = desc->variant >= 0 && desc->variant < kNumVariants ? desc->variant : kDefaultVariant;
   p->num_sms = desc->num_sms;
   if (p->num_sms <= 0) {
@@ -495,7 +513,17 @@ int w3d_plan_exchange_stats(W3dPlan* p, unsigned long long out[W3D_XSTAT_WORDS],
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   CUDA_TRY(cudaMemcpyAsync(&h, static_cast<char*>(p->d.workspace) + kXStatOffset, sizeof(h), cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
-  out[0] = h.sum_wait; out[1] = h.sum_copy; out[2] = h.launches; out[3] = h.max_wait; out[4] = h.max_copy;
+  // (per-launch maxima that no later launch has folded yet: the last launch of a deferred-release plan)
+  const unsigned long long pw = std::max(h.cur_wait[0], h.cur_wait[1]), pc = std::max(h.cur_copy[0], h.cur_copy[1]);
+  out[0] = h.sum_wait + pw; out[1] = h.sum_copy + pc; out[2] = h.launches;
+  out[3] = std::max(h.max_wait, pw); out[4] = std::max(h.max_copy, pc);
+  return W3D_OK;
+}
+
+int w3d_plan_set_timeline(W3dPlan* p, unsigned long long* dev_buf, int capacity) {
+  if (!p) return fail(W3D_EINVAL, "null plan");
+  p->timeline = dev_buf;
+  p->timeline_cap = dev_buf ? capacity : 0;
   return W3D_OK;
 }
 
@@ -605,20 +633,11 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const*
     for (int d = 0; d < 3; ++d)
       if ((p->d.peer[d * 2].active || p->d.peer[d * 2 + 1].active) && p->g.n[d] < 2)
         return fail(W3D_EINVAL, "wide halo needs at least 2 unknowns along the axis with neighbours");
-  // variant: given, or the cheaper of the measured 64x32 default and the 64x30 tiling by the wave model
-  // (64x30 only wins when it removes a partial wave, e.g. 511 rows: 16 -> 18 tiles, 128 -> 144 CTAs)
-  if (pair_variant >= 0 && pair_variant < kNumPairVariants) {
-    p->pair_variant = pair_variant;
-    plan_pair_tiles(p, p->pair_variant, zchunk, &p->ptile);
-  } else {
-    const int cand[2] = {4, 8};
-    double best = 1e300;
-    for (int c = 0; c < 2; ++c) {
-      TileGeom t;
-      const double cost = plan_pair_tiles(p, cand[c], zchunk, &t) * (c == 0 ? 1.0 : 1.03);   // ties and near-ties: keep the default
-      if (cost < best) { best = cost; p->pair_variant = cand[c]; p->ptile = t; }
-    }
-  }
+  // variant: given, or the best of the measured sweep.  (The 64x30 tilings put 144 instead of 128 CTAs on
+  // the 148 SMs for 511 rows, but with 12 instead of 16 warps per SM each CTA is as slow as a 64x32 one:
+  // measured 0.0626 vs 0.0613 ms per step on the 511 x 511 x 64 block — profiles/pair_schedule.md.)
+  p->pair_variant = (pair_variant >= 0 && pair_variant < kNumPairVariants) ? pair_variant : 4;
+  plan_pair_tiles(p, p->pair_variant, zchunk, &p->ptile);
   if (p->pair_mode == W3D_PAIR_WIDE && p->step_depth != 2) {
     // the single-step kernel keeps the wide halo alive too (it ships two layers), so single steps
     // and pair passes can follow each other in any order
@@ -654,7 +673,7 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const*
     std::vector<int> face, waiters, rest;
     for (int w = 0; w < p->pn_ctas; ++w) {
       const int tx = w % t.ntx, ty = (w / t.ntx) % t.nty, ch = w / (t.ntx * t.nty);
-      const int lo[3] = {t.x0 + tx * v.tx, t.lo[1] + ty * v.ty, t.lo[2] + ch * t.zc};
+      const int lo[3] = {t.x0 + tx * v.tx, pair_tile_y0(t, ty, v.ty), t.lo[2] + ch * t.zc};
       const int hi[3] = {lo[0] + v.tx, lo[1] + v.ty, std::min(lo[2] + t.zc, t.hi[2])};
       if (face_mask_host(p->d, p->g.n, lo, hi, depth)) face.push_back(w);
       else if (face_mask_host(p->d, p->g.n, lo, hi, 2)) waiters.push_back(w);
@@ -729,6 +748,7 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
   const int ship = wide ? out2 : out1;
   P.nxt = p->arr[ship];
   P.halo_depth = wide ? 2 : 1;
+  P.zpush = wide ? ((p->d.peer[4].active ? 1 : 0) | (p->d.peer[5].active ? 2 : 0)) : 0;
   P.n_face_ctas = p->pn_face_ctas;
   P.use_flags = p->any_peer ? 1 : 0;
   for (int f = 0; f < 6; ++f) {
@@ -744,9 +764,14 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
   P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
   P.status = p->d.status;
   P.xstat = reinterpret_cast<XStat*>(static_cast<char*>(p->d.workspace) + kXStatOffset);
+  P.tl = (p->timeline && s >= 0 && s < p->timeline_cap) ? p->timeline + 2 * (size_t)s : nullptr;
+  P.seq = p->launch_seq++;
+  P.defer_release = wide ? 1 : 0;
   P.level = (unsigned long long)s;
   P.release = (unsigned long long)s + (wide ? 2ull : 1ull);
   P.timeout_ns = (unsigned long long)(p->d.spin_timeout_ms > 0 ? p->d.spin_timeout_ms : 10000) * 1000000ull;
+  // (programmatic dependent launch was tried here: the graph's launch gap is 1.5 us and with one CTA per SM the
+  // successor has nowhere to start early — no gain, profiles/pair_schedule.md)
   v.kernel<<<p->pn_ctas, v.threads, v.smem, static_cast<cudaStream_t>(stream)>>>(P);
   CUDA_TRY(cudaGetLastError());
   ++p->launches;

@@ -187,6 +187,13 @@ int w3d_step_fused_on(W3dPlan* plan, int s, int cur, int prev, double a, double 
 #define W3D_XSTAT_WORDS 5
 int w3d_plan_exchange_stats(W3dPlan* plan, unsigned long long out[W3D_XSTAT_WORDS], void* stream);
 
+/* Device timeline (tracing): dev_buf holds `capacity` pairs of 64-bit %globaltimer stamps.  A step
+ * or pair launch whose input level is s < capacity records into pair s: [2s] = earliest start of
+ * any of its CTAs (atomicMin), [2s+1] = latest end (atomicMax).  The caller fills the buffer with
+ * (UINT64_MAX, 0) pairs beforehand; NULL switches recording off.  The difference between one
+ * launch's end and the next one's start is the launch gap that no event timing can see. */
+int w3d_plan_set_timeline(W3dPlan* plan, unsigned long long* dev_buf, int capacity);
+
 /* NCCL-baseline helpers (K5): contiguous face buffers of the unknowns of the two
  * other axes, fastest index first.  ghost=0 packs/unpacks the edge layer of
  * unknowns, ghost=1 the ghost layer. */

@@ -15,7 +15,8 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 NATIVE = Path(__file__).resolve().parent / "_native"
 CPU_LIB = NATIVE / "libwave3d_cpu.so"
-CUDA_LIB = NATIVE / "libwave3d_b200.so"
+# W3D_CUDA_LIB: load an alternative build of the CUDA library (kernel experiments: scripts/build_variants.sh)
+CUDA_LIB = Path(os.environ["W3D_CUDA_LIB"]).resolve() if os.environ.get("W3D_CUDA_LIB") else NATIVE / "libwave3d_b200.so"
 
 
 def _run_make(target: str, quiet: bool = True) -> None:

@@ -67,6 +67,7 @@ def lib() -> C.CDLL:
     l.w3d_step_fused.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
     l.w3d_step_fused_on.argtypes = [vp, C.c_int, C.c_int, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
     l.w3d_plan_pair_mode.argtypes = [vp]
+    l.w3d_plan_set_timeline.argtypes = [vp, vp, C.c_int]
     l.w3d_plan_exchange_stats.argtypes = [vp, C.POINTER(C.c_ulonglong), vp]
     l.w3d_step_tma.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, i32p, i32p, vp, C.c_int, vp]
     l.w3d_step_box.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, i32p, i32p, vp, C.c_int, vp]
@@ -248,6 +249,12 @@ class CudaPlan:
         for f, (p0, p1) in (peer_aux or {}).items():
             table[2 * f], table[2 * f + 1] = p0, p1
         check(lib().w3d_plan_enable_pairs(self._h, aux0.data_ptr(), aux1.data_ptr(), table, pair_variant, zchunk))
+
+    def set_timeline(self, buf: Optional[torch.Tensor]) -> None:
+        """buf: int64 tensor of shape (capacity, 2) pre-filled with (INT64 max as uint64 max, 0), or None."""
+        self._timeline = buf
+        check(lib().w3d_plan_set_timeline(self._h, None if buf is None else buf.data_ptr(),
+                                          0 if buf is None else buf.shape[0]))
 
     @property
     def pair_mode(self) -> int:

@@ -144,6 +144,10 @@ class FusedSolver:
                                   err_table_peer_ptrs=[base_ptrs[r] + _FLAG_BYTES for r in range(self.world)
                                                        if r != self.rank] if self.world > 1 else [],
                                   ghost_depth=gd)
+        # device timeline: (earliest CTA start, latest CTA end) per launch, indexed by input level
+        self._tl_buf = torch.zeros((p.K + 1, 2), dtype=torch.int64, device=self.device)
+        self._tl_buf[:, 0] = -1
+        self.plan.set_timeline(self._tl_buf)
         self.ct = time_table(p)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.kernel_launches = 0
@@ -349,6 +353,23 @@ class FusedSolver:
         return self.field(self.level & 1)
 
     # -- tracing ---------------------------------------------------------------
+    def device_timeline(self) -> List[Tuple[int, float, float]]:
+        """One whole run with %globaltimer stamps taken inside the kernels.
+
+        Returns [(input level, start_us, end_us)] per launch on this rank, relative to the first
+        start: start = earliest CTA of the launch, end = latest CTA.  end(p) -> start(p+1) is the
+        launch gap; what lies between start and end includes the flag waits (see exchange_stats).
+        Uses the captured CUDA graph if there is one (the stamp buffer is part of every launch)."""
+        self.init()
+        self._tl_buf[:, 0] = -1           # 0xffff... = UINT64_MAX for the device-side atomicMin
+        self._tl_buf[:, 1] = 0
+        self.run_steps()
+        self.barrier()
+        h = self._tl_buf.cpu()
+        rows = [(s, int(h[s, 0]), int(h[s, 1])) for s in range(h.shape[0]) if int(h[s, 1]) != 0]
+        t0 = min(r[1] for r in rows)
+        return [(s, (a - t0) / 1e3, (b - t0) / 1e3) for s, a, b in rows]
+
     def profile_steps(self) -> List[float]:
         """Device time per step (ms, CUDA events, eager launches; max over ranks).
 
