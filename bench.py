@@ -5,14 +5,25 @@ Metric (BASELINE.json): wall time (s) and GLUP/s at 512^3 K=20, device-timed, ma
 over ranks.  The reference's published numbers are 0.752 s / 3.55 GLUP/s on one
 P100 and 0.505 s / 5.28 GLUP/s on two (readme.md:99-100; report.pdf p.16 §4.4).
 
-A bench "step" is one time step of the scheme (one fused kernel launch per GPU:
-stencil + in-kernel P2P halo exchange + error epilogue).  ``--steps K`` runs the
+A bench "step" is one time step of the scheme.  The default path advances two
+steps per kernel launch (stencil x2 + in-kernel P2P halo exchange + error
+epilogue); ``--no-pair`` runs one launch per step.  ``--steps K`` runs the
 reference's workload exactly when K = 20: Taylor step + 19 leapfrog steps, error
-norms on every 2nd step like the reference prints them.  Timed region: K steps,
-CUDA events, barrier + synchronize on both sides, max over ranks; repeated
-``--reps`` times (each repetition re-initialises the field outside the timed
-region) and the median repetition is reported.  The two 1.16 GB field arrays are
-far larger than the 126 MB L2, so no flush is needed between iterations.
+norms on every 2nd step like the reference prints them.  Timed region (``value``,
+``ms_per_step``, ``loop_s``): K steps, CUDA events, barrier + synchronize on both
+sides, max over ranks; repeated ``--reps`` times (each repetition re-initialises
+the field outside the timed region) and the median repetition is reported.
+``total_s`` adds the initialisation (layer 0, flag reset, barrier), which is what
+the reference's "total" column contains; ``vs_baseline`` is computed from it.
+The field arrays are far larger than the 126 MB L2 at one GPU; at 8 GPUs the
+per-GPU working set (4 x 0.14 GB) is still 4.5 L2 sizes, and every pass reads
+arrays that were written two passes earlier, so no flush is needed.
+
+The same-box comparator: after the fused timing the straightforward build the
+north star asks for — pack -> NCCL send/recv -> unpack -> one-pass step kernel ->
+error all-gather, the whole K-step loop in one CUDA graph so that it is not
+limited by Python — runs at the same N / K / decomposition and is printed as
+``baseline_nccl`` with ``vs_nccl``.
 
 ``--impl reference``: the reference tree ships no source (only readme.md and
 report.pdf), so it cannot be installed; prints the "unavailable" line.
@@ -96,6 +107,57 @@ def reference_arm() -> int:
     return 0
 
 
+def validate_trace(p, trace, every):
+    """Every reporting line against the strictest oracle available.
+
+    Headline config (512^3, L=1, tau=1e-3, Dirichlet, every 2nd step): the reference's published
+    ten-line trace, |dMax| <= 5e-15 absolute and 1e-6 relative on L2 (report.pdf p.15-16; the
+    tolerance the golden file supports).  Anything else: the closed-form
+    recurrence oracle on every line, round-off allowance growing with the step number."""
+    from mpi_cuda_b200.models.analytic import oracle_errors
+    from mpi_cuda_b200.utils import report
+    if not trace:
+        return None, None
+    headline = (tuple(p.N) == (512, 512, 512) and tuple(p.L) == (1.0, 1.0, 1.0) and abs(p.tau - 1e-3) < 1e-18
+                and p.bc == "ddd" and every == 2 and p.K <= 20)
+    if headline:
+        gold = {g[0]: g for g in report.GOLDEN_512}
+        ok = all(r[0] in gold and abs(r[2] - gold[r[0]][2]) <= 5e-15 and abs(r[3] - gold[r[0]][3]) <= 1e-6 * gold[r[0]][3]
+                 for r in trace) and len(trace) == min(p.K, 20) // 2
+        return bool(ok), "published 512^3 trace, all %d lines, |dMax| <= 5e-15, L2 rel 1e-6" % len(trace)
+    ok = True
+    for n, _, mx, l2 in trace:
+        omx, ol2 = oracle_errors(p, n)
+        tol = 5e-15 * max(1.0, n / 20.0)
+        ok = ok and abs(mx - omx) <= tol + 1e-9 * omx and abs(l2 - ol2) <= tol + 1e-6 * ol2
+    return bool(ok), "closed-form oracle, all %d lines, |dMax| <= 5e-15 * max(1, n/20)" % len(trace)
+
+
+def nccl_loop(p, dims, device, args, reps, sampler):
+    """The NCCL-halo build: K steps per repetition, graph replay when NCCL can be captured."""
+    import statistics as st
+    from mpi_cuda_b200.parallel.exchange import CudaBlockOps, ExchangeSolver
+    s = ExchangeSolver(p, dims, lambda pp, b: CudaBlockOps(pp, b, device, args.variant, args.zchunk),
+                       every=args.every, backend_name="nccl")
+    graph = s.capture()
+    times, trace = [], []
+    if not graph:
+        s.run(time_phases=False)
+    if sampler is not None:
+        sampler.start()
+    l0 = s.ops.plan.launches
+    for _ in range(reps):
+        if graph:
+            t, trace = s.run_graph()
+            times.append(t * 1e3)
+        else:
+            r = s.run(time_phases=False)
+            times.append(r.phases["loop"] * 1e3)
+            trace = r.trace
+    launches = (s.ops.plan.launches - l0) // reps if not graph else s.launches_per_run
+    return times, trace, launches, graph
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -113,6 +175,7 @@ def main() -> int:
     ap.add_argument("--reps", type=int, default=7)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-nccl-baseline", action="store_true", help="skip the same-box NCCL comparator run")
     ap.add_argument("--every", type=int, default=2)
     ap.add_argument("--pair", dest="pair", action="store_true", default=True,
                     help="temporal blocking: two time steps per pass over memory (default)")
@@ -168,13 +231,16 @@ def main() -> int:
         barrier()
         if s.use_graph:
             s.capture()
-        times = []
+        times, init_times = [], []
         launches0 = s.kernel_launches
         sampler.start()
         nreps = args.reps
         rep = 0
         while rep < nreps:
-            s.init()                       # untimed: layer 0, flags reset, barrier
+            barrier()
+            t_i0 = time.perf_counter()
+            s.init()                       # not in the loop time: layer 0, flags reset, barrier (timed for total_s)
+            init_times.append(max_over_ranks(time.perf_counter() - t_i0))
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             barrier()
             e0.record()
@@ -210,7 +276,7 @@ def main() -> int:
                 barrier()
                 t0 = time.perf_counter()
                 sess.start()               # tables H2D from pinned memory + init kernel + barrier
-                lag = 2 if s.pair else 1       # keep one launch in flight while earlier results are read
+                lag = 4 if s.pair else 2       # keep two launches in flight while earlier results are read
                 for n in range(1, K + 1):
                     sess.step_async(n)
                     if n > lag:
@@ -225,31 +291,34 @@ def main() -> int:
                    "h2d_bytes_per_step": sess.H2D_BYTES_PER_STEP + sess.table_bytes / K,
                    "d2h_bytes_per_step": sess.D2H_BYTES_PER_STEP,
                    "includes": "analytic tables H2D (pinned) + layer-0 init + K x (8 B H2D of the step input, fused step, "
-                               "16 B D2H of the step result, host waits for every result; one step kept in flight)"}
+                               "16 B D2H of the step result, host waits for every result; two launches kept in flight)"}
     else:
-        from mpi_cuda_b200.parallel.exchange import CudaBlockOps, ExchangeSolver
-        s = ExchangeSolver(p, dims, lambda pp, b: CudaBlockOps(pp, b, device, args.variant, args.zchunk),
-                           every=args.every, backend_name="nccl")
-        s.run(time_phases=False)
-        times = []
-        sampler.start()
-        l0 = s.ops.plan.launches
-        for _ in range(args.reps):
-            r = s.run(time_phases=False)
-            times.append(r.phases["loop"] * 1e3)
+        times, trace, launches, nccl_graph = nccl_loop(p, dims, device, args, args.reps, sampler)
         clocks = sampler.stop()
-        launches = (s.ops.plan.launches - l0) // args.reps
-        trace = r.trace
+        init_times = [0.0]
+        extra["nccl_cuda_graph"] = nccl_graph
         e2e = None
 
     t_ms = statistics.median(times)
     glups = p.updates / (t_ms / 1e3) / 1e9
-    # correctness guard: the error at the last reporting step must match the closed form
-    valid = None
-    if trace:
-        n, _, mx, l2 = trace[-1]
-        omx, ol2 = oracle_errors(p, n)
-        valid = bool(abs(mx - omx) <= 1e-13 + 1e-5 * omx and abs(l2 - ol2) <= 1e-13 + 1e-5 * ol2)
+    t_init_s = statistics.median(init_times)
+    total_s = t_init_s + t_ms / 1e3
+    valid, valid_against = validate_trace(p, trace, args.every)
+    # ---- same-box comparator: the NCCL-halo build at the same N / K / decomposition ----
+    baseline_nccl = None
+    if args.backend == "fused" and not args.no_nccl_baseline:
+        try:
+            del s
+            torch.cuda.empty_cache()
+            b_times, b_trace, b_launches, b_graph = nccl_loop(p, dims, device, args, max(5, min(args.reps, 30)), None)
+            b_ms = statistics.median(b_times)
+            b_valid, _ = validate_trace(p, b_trace, args.every)
+            baseline_nccl = {"ms_per_step": b_ms / K, "glups": p.updates / (b_ms / 1e3) / 1e9, "cuda_graph": b_graph,
+                             "launches": b_launches, "validated_vs_oracle": b_valid,
+                             "what": "pack -> NCCL send/recv -> unpack -> one-pass TMA step kernel -> error all-gather "
+                                     "on reporting steps; whole loop in one CUDA graph, no host sync inside"}
+        except Exception as e:                      # the comparator must never take the headline down with it
+            baseline_nccl = {"error": repr(e)[:300]}
     pub = PUBLISHED_GLUPS.get(world, PUBLISHED_GLUPS[2])
     from mpi_cuda_b200.parallel.decomp import plan_all
     from mpi_cuda_b200.utils import roofline
@@ -259,15 +328,19 @@ def main() -> int:
     bytes_per_node, nodes_per_gpu = rf["bytes_per_node_per_step"], rf["nodes_per_gpu"]
     bytes_per_gpu, halo_bytes, t_roof_ms = rf["bytes_per_gpu_per_step"], rf["halo_bytes_per_gpu_per_step"], rf["roofline_ms_per_step"]
     out = {
-        "metric": "GLUP/s at %s grid, K=%d steps, fp64, device-timed max over ranks (wall_s = total)" % (grid_name, K),
+        "metric": "GLUP/s at %s grid, K=%d steps, fp64, device-timed K-step loop, max over ranks "
+                  "(loop_s = the loop; total_s = init + loop, the reference's 'total')" % (grid_name, K),
         "value": glups, "unit": "GLUP/s", "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": t_ms / K, "wall_s": t_ms / 1e3, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": glups / pub, "dtype": "fp64", "data": "synthetic (analytic-solution initial layers)",
+        "ms_per_step": t_ms / K, "loop_s": t_ms / 1e3, "init_s": t_init_s, "total_s": total_s,
+        "higher_is_better": True, "scaling": "strong",
+        # like for like: the published GLUP/s is updates / published TOTAL time, so ours uses total_s too
+        "vs_baseline": (p.updates / total_s / 1e9) / pub, "vs_baseline_loop_only": glups / pub,
+        "dtype": "fp64", "data": "synthetic (analytic-solution initial layers)",
         "config": {"model": "wave3d leapfrog 7-point", "grid": grid_name, "global_batch": p.n_unknowns,
                    "seq_len": K, "parallelism": f"spatial {dims[0]}x{dims[1]}x{dims[2]}", "backend": args.backend,
                    "bc": args.bc, "L": list(p.L), "temporal_blocking": bool(args.pair), "tau": args.tau, "report_every": args.every,
-                   "l2_policy": "inputs larger than L2 (%d x %.2f GB fields per GPU vs 126 MB L2), no flush"
-                                % (4 if pair_mode else 2, nodes_per_gpu * 8 / 1e9),
+                   "l2_policy": "inputs larger than L2 (%d x %.2f GB fields per GPU vs 126 MB L2; every pass reads arrays "
+                                "written two passes earlier), no flush" % (4 if pair_mode else 2, nodes_per_gpu * 8 / 1e9),
                    "reps": args.reps, "rep_ms": [round(t, 4) for t in times],
                    "cuda_graph": (not args.no_graph) and args.backend == "fused",
                    "published_baseline": {"glups": pub, "wall_s": PUBLISHED_WALL_S.get(world, 0.505),
@@ -277,9 +350,13 @@ def main() -> int:
                      "fraction_of_roofline": t_roof_ms / (t_ms / K), "of": "measured" if peaks else "fallback",
                      "bytes_per_node_per_step": bytes_per_node,
                      "vs_single_pass_roofline": rf["single_pass_roofline_ms_per_step"] / (t_ms / K)},
-        "clocks": clocks, "gpu_launches": launches, "validated_vs_oracle": valid,
+        "clocks": clocks, "gpu_launches": launches, "validated_vs_oracle": valid, "validated_against": valid_against,
         "last_error_line": trace[-1] if trace else None,
     }
+    if baseline_nccl is not None:
+        out["baseline_nccl"] = baseline_nccl
+        if "glups" in baseline_nccl:
+            out["vs_nccl"] = glups / baseline_nccl["glups"]
     if e2e is not None:
         out["e2e"] = e2e
     out.update(extra)

@@ -389,7 +389,7 @@ __device__ __noinline__ void face_cta_done(const PT& P, unsigned long long wait_
   const int slot = P.seq & 1;
   if (P.xstat) {
     atomicMax(&P.xstat->cur_wait[slot], wait_ns);
-    atomicMax(&P.xstat->cur_copy[slot], globaltimer_ns() - t_copy0);
+    if (t_copy0) atomicMax(&P.xstat->cur_copy[slot], globaltimer_ns() - t_copy0);
     __threadfence();
   }
   const unsigned done = atomicAdd(P.shell_counter, 1u);
@@ -699,12 +699,15 @@ __global__ void __launch_bounds__(256) box_step_kernel(const __grid_constant__ S
 __global__ void __launch_bounds__(1024, 1) fixup_kernel(const __grid_constant__ StepParams P) {
   __shared__ double red[66];
   double mx = 0.0, s2 = 0.0;
+  unsigned long long wait_ns = 0ull, t0 = 0ull;
+  if (P.tl && threadIdx.x == 0) atomicMin(P.tl, globaltimer_ns());
   if (P.use_flags) {
     if (threadIdx.x == 0) {
       int mask = 0;
       for (int f = 0; f < 6; ++f)
         if (P.peer[f].active) mask |= 1 << f;
-      wait_peer_flags(P, mask);
+      wait_ns = wait_peer_flags(P, mask);
+      t0 = globaltimer_ns();
     }
     __syncthreads();
   }
@@ -712,7 +715,7 @@ __global__ void __launch_bounds__(1024, 1) fixup_kernel(const __grid_constant__ 
                    P.boxes.prefix[P.boxes.nboxes], P.use_flags != 0, mx, s2);
   if (P.use_flags) {
     __syncthreads();
-    if (threadIdx.x == 0) face_cta_done(P);
+    if (threadIdx.x == 0) face_cta_done(P, wait_ns, t0);    // (the whole shell pass counts as halo copy-out time)
   }
   publish_error(P.err, mx, s2, red);
 }

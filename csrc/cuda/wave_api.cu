@@ -149,6 +149,7 @@ struct W3dPlan {
   bool pair_ready;
   int pair_mode;                   // W3D_PAIR_LOCAL / WIDE / FIXUP
   int step_depth;                  // halo layers the single-step kernel ships: 1, or 2 in wide-halo plans
+  bool defer;                      // wide halo, (nearly) all pair CTAs are face CTAs: flags are published at the next launch's entry
   int launch_seq;                  // launches issued through this plan (parity selects the XStat slot)
   unsigned long long* timeline;    // optional device buffer of (start, end) stamps per launch, indexed by level
   int timeline_cap;
@@ -310,7 +311,7 @@ void fill_common(const W3dPlan* p, StepParams* P, int s, double a, double b, dou
   P->release = (unsigned long long)s + 1ull;
   P->halo_depth = p->step_depth;
   P->seq = const_cast<W3dPlan*>(p)->launch_seq++;
-  P->defer_release = p->pair_mode == W3D_PAIR_WIDE ? 1 : 0;
+  P->defer_release = p->defer ? 1 : 0;
   P->tl = (p->timeline && s >= 0 && s < p->timeline_cap) ? p->timeline + 2 * (size_t)s : nullptr;
   P->xstat = reinterpret_cast<XStat*>(static_cast<char*>(p->d.workspace) + kXStatOffset);
   P->timeout_ns = (unsigned long long)(p->d.spin_timeout_ms > 0 ? p->d.spin_timeout_ms : 10000) * 1000000ull;
@@ -376,6 +377,7 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
   p->timeline = nullptr;
   p->timeline_cap = 0;
   p->launch_seq = 0;
+  p->defer = false;
   p->variant = desc->variant >= 0 && desc->variant < kNumVariants ? desc->variant : kDefaultVariant;
   p->num_sms = desc->num_sms;
   if (p->num_sms <= 0) {
@@ -680,6 +682,14 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const*
       else rest.push_back(w);
     }
     p->pn_face_ctas = (int)face.size();
+    // A system fence + counter in every face CTA at the end of the pass costs 4.8 us when every CTA is a face
+    // CTA (one-wave launches on thin slabs): the flags are published by the NEXT launch at its entry instead
+    // (entry_release, kernels.cuh).
+    // Measured (2 GPUs, 512^3 and 1024^3): publishing at the next launch's entry is as good or better even when
+    // the face CTAs are a minority, so it is the rule for every wide-halo plan; W3D_DEFER=0 switches back to the
+    // in-kernel release for experiments.
+    const char* de = std::getenv("W3D_DEFER");
+    p->defer = p->pair_mode == W3D_PAIR_WIDE && !(de && de[0] == '0');
     face.insert(face.end(), waiters.begin(), waiters.end());
     face.insert(face.end(), rest.begin(), rest.end());
     CUDA_TRY(cudaMemcpy(p->order_dev + W3D_MAX_PARTIALS, face.data(), face.size() * sizeof(int),
@@ -689,8 +699,9 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const*
   const size_t used = std::strlen(p->text);
   static const char* kModeName[3] = {"no neighbours", "wide halo: 1 launch + 1 handshake per 2 steps", "fix-up pass: 2 launches per 2 steps"};
   snprintf(p->text + used, sizeof(p->text) - used,
-           " || %s (%d thr, %d B smem): tiles %dx%d zc %d chunks %d -> %d CTAs, %d face CTAs [%s]", v.name, v.threads,
-           v.smem, t.ntx, t.nty, t.zc, t.nchunks, p->pn_ctas, p->pn_face_ctas, kModeName[p->pair_mode]);
+           " || %s (%d thr, %d B smem): tiles %dx%d zc %d chunks %d -> %d CTAs, %d face CTAs [%s%s]", v.name, v.threads,
+           v.smem, t.ntx, t.nty, t.zc, t.nchunks, p->pn_ctas, p->pn_face_ctas, kModeName[p->pair_mode],
+           p->pair_mode != W3D_PAIR_WIDE ? "" : p->defer ? ", flags published at the next launch's entry" : ", flags released by the last face CTA");
   return W3D_OK;
 }
 
@@ -766,7 +777,7 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
   P.xstat = reinterpret_cast<XStat*>(static_cast<char*>(p->d.workspace) + kXStatOffset);
   P.tl = (p->timeline && s >= 0 && s < p->timeline_cap) ? p->timeline + 2 * (size_t)s : nullptr;
   P.seq = p->launch_seq++;
-  P.defer_release = wide ? 1 : 0;
+  P.defer_release = p->defer ? 1 : 0;
   P.level = (unsigned long long)s;
   P.release = (unsigned long long)s + (wide ? 2ull : 1ull);
   P.timeout_ns = (unsigned long long)(p->d.spin_timeout_ms > 0 ? p->d.spin_timeout_ms : 10000) * 1000000ull;

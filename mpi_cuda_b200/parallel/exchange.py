@@ -166,6 +166,74 @@ class ExchangeSolver:
         self.recvbuf = {(d, s): self.ops.recv_buffer(d) for d in range(3) for s in range(2)
                         if self.blk.nbr[d][s] >= 0 and self.blk.nbr[d][s] != self.rank}
         self.ct = time_table(p)
+        self.graph = None                 # CUDA graph of the whole K-step loop (GPU ops only, see capture())
+        self._err_gather = None
+
+    # -- the baseline's fair shot: the whole loop in one CUDA graph -------------
+    def _loop_body(self) -> None:
+        """K steps on the current stream, no host synchronisation: exchange -> step -> on reporting
+        steps ONE all-gather of this rank's (max, sum) pair (combined on the host after the loop)."""
+        p, ops = self.p, self.ops
+        for n in range(1, p.K + 1):
+            s = n - 1
+            a, b, cs = step_coeffs(n)
+            want = n % self.every == 0
+            self.exchange(s & 1)
+            ops.step(s, a, b, cs, float(self.ct[n]), want, n, None)
+            if want:
+                e = ops.local_error(n)
+                if self.world > 1:
+                    dist.all_gather_into_tensor(self._err_gather[n], e, group=self.group)
+                else:
+                    self._err_gather[n].copy_(e)
+
+    def capture(self) -> bool:
+        """Capture the K-step loop (pack, NCCL send/recv, unpack, step, error all-gather) in a CUDA graph.
+
+        Returns False (and leaves the solver in eager mode) if NCCL refuses to be captured."""
+        if self.graph is not None:
+            return True
+        dev = self.ops.device
+        self._err_gather = torch.zeros((self.p.K + 1, 2 * self.world), dtype=torch.float64, device=dev)
+        self.ops.init()
+        l0 = self.ops.plan.launches
+        self._loop_body()                    # warm-up outside capture (lazy module load, NCCL channels)
+        self.launches_per_run = self.ops.plan.launches - l0
+        torch.cuda.synchronize(dev)
+        if self.world > 1:
+            dist.barrier(self.group)
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._loop_body()
+            self.graph = g
+        except Exception as e:               # pragma: no cover - depends on the NCCL build
+            self.graph = None
+            self.capture_error = repr(e)
+            torch.cuda.synchronize(dev)
+            return False
+        torch.cuda.synchronize(dev)
+        return True
+
+    def run_graph(self) -> Tuple[float, List[Tuple[int, float, float, float]]]:
+        """One whole run by graph replay; returns (loop seconds on the device, max over ranks; trace)."""
+        p, dev = self.p, self.ops.device
+        self.ops.init()
+        torch.cuda.synchronize(dev)
+        if self.world > 1:
+            dist.barrier(self.group)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        self.graph.replay()
+        ev1.record()
+        torch.cuda.synchronize(dev)
+        t = torch.tensor([ev0.elapsed_time(ev1) / 1e3], dtype=torch.float64, device=dev)
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        g = self._err_gather.cpu().view(p.K + 1, self.world, 2)
+        trace = [(n, n * p.tau, float(g[n, :, 0].max()), math.sqrt(float(g[n, :, 1].sum()) / p.n_unknowns))
+                 for n in range(1, p.K + 1) if n % self.every == 0]
+        return float(t.item()), trace
 
     # -- halo exchange of the array with the given parity ---------------------
     def exchange(self, parity: int) -> None:

@@ -168,16 +168,30 @@ class FusedSolver:
         if self.world > 1:
             dist.barrier(self.group)
 
-    def init(self) -> None:
+    def device_barrier(self) -> None:
+        """All ranks' streams meet here WITHOUT the host: a signal-pad barrier kernel of the symmetric-memory
+        handle, enqueued on the current stream (falls back to the host barrier where the handle has none)."""
+        if self.world == 1:
+            return
+        try:
+            self.symm.barrier(channel=0)
+        except (AttributeError, TypeError, RuntimeError):
+            self.barrier()
+
+    def init(self, host_sync: bool = True) -> None:
         """Layer 0 everywhere (ghosts included), zero second array, flags reset.
 
         All ranks must have finished this before any rank's first step may push
-        into their ghosts, hence the barrier."""
+        into their ghosts, hence the barrier — on the host by default, or (``host_sync=False``)
+        a device-side barrier on the stream, so that the host can go on enqueuing steps."""
         self.plan.init(zero_second=self._zero_second)
         self.table[self.rank].zero_()                    # only my own row: peers clear theirs
         self.level, self._cur, self._prev = 0, 0, 1
         self.final_index = 0
-        self.barrier()
+        if host_sync:
+            self.barrier()
+        else:
+            self.device_barrier()
 
     def step(self, n: int, want_err: bool = True) -> None:
         """Produce time level n (n = 1 is the Taylor step) with the one-pass-per-step kernel.
@@ -464,7 +478,13 @@ class StreamingSession:
         self.ct_host = torch.from_numpy(solver.ct.copy()).pin_memory()
         self.ct_dev = torch.zeros(p.K + 2, dtype=torch.float64, device=solver.device)
         self.err_host = torch.zeros((p.K + 1, _SLOTS, 2), dtype=torch.float64).pin_memory()
+        self._err_np = self.err_host.numpy()             # same memory: reading a result costs no torch dispatch
+        # per-step views made once (slicing a tensor costs more than the 8-byte copy it feeds)
+        self._ct_src = [self.ct_host[n: n + 1] for n in range(p.K + 1)]
+        self._ct_dst = [self.ct_dev[n: n + 1] for n in range(p.K + 1)]
         self._done: Dict[int, torch.cuda.Event] = {}
+        self.tab_host = [torch.from_numpy(t).pin_memory()
+                         for t in local_tables(p, solver.blk, ghosts=2 if solver.pair else 1)]
         solver.plan.set_ct_table(self.ct_dev)
 
     def close(self) -> None:
@@ -473,11 +493,9 @@ class StreamingSession:
     def start(self) -> None:
         """Upload the analytic tables from pinned host memory and build layer 0."""
         s = self.s
-        from .decomp import local_tables
-        self.tab_host = [torch.from_numpy(t).pin_memory() for t in local_tables(s.p, s.blk, ghosts=2 if s.pair else 1)]
         for dst, src in zip(s.tab_full, self.tab_host):
             dst.copy_(src, non_blocking=True)
-        s.init()
+        s.init(host_sync=False)
 
     @property
     def table_bytes(self) -> int:
@@ -490,7 +508,7 @@ class StreamingSession:
         uploads its input, the call for the second one launches the pass and reads both back;
         the last step of an odd-length run goes alone."""
         s = self.s
-        self.ct_dev[n: n + 1].copy_(self.ct_host[n: n + 1], non_blocking=True)
+        self._ct_dst[n].copy_(self._ct_src[n], non_blocking=True)
         if s.pair:
             if n == s.level + 2:
                 s.pair_advance(s.level, force_err=True)
@@ -516,8 +534,8 @@ class StreamingSession:
         if n not in self._done:
             raise RuntimeError(f"step {n} has not been launched yet (pair mode launches two steps at a time)")
         self._done.pop(n).synchronize()
-        e = self.err_host[n]
-        return float(e[:, 0].max()), float(e[:, 1].sum())
+        e = self._err_np[n]
+        return max(float(e[0, 0]), float(e[1, 0])), float(e[0, 1]) + float(e[1, 1])
 
     def step(self, n: int) -> Tuple[float, float]:
         """Synchronous single step (not available in pair mode, where steps come in twos)."""

@@ -93,7 +93,9 @@ def test_gloo_rank_count_invariance(world, dims, bc):
 
 def test_auto_decomposition_policy():
     assert decomp.parse_dims("auto", 8, (511, 511, 511)) == (1, 1, 8)      # 63 planes per rank: slab
-    assert decomp.parse_dims("auto", 8, (1023, 1023, 1023)) == (1, 2, 4)   # large grid: blocks
-    assert decomp.parse_dims("auto", 8, (255, 255, 255)) == (1, 2, 4)      # slabs would be too thin
+    assert decomp.parse_dims("auto", 8, (1023, 1023, 1023)) == (1, 1, 8)   # one axis with neighbours: one launch per pair
+    assert decomp.parse_dims("auto", 8, (2047, 2047, 2047)) == (1, 1, 8)
+    assert decomp.parse_dims("auto", 8, (255, 255, 255)) == (1, 1, 8)
+    assert decomp.parse_dims("auto", 8, (63, 63, 63)) == (1, 2, 4)         # slabs would be thinner than 8 planes
     assert decomp.parse_dims("auto", 1, (511, 511, 511)) == (1, 1, 1)
     assert decomp.parse_dims("auto", 4) == (1, 2, 2)
