@@ -45,8 +45,13 @@
 
 namespace w3d {
 
-template <int TX, int RPT, int RG, int STAGES, int MINB = 1>
+// CLY = 2: thread-block clusters of two CTAs whose tiles are neighbours in y.  Each CTA leaves out the
+// level-1 ring row on its partner's side and reads those values — the partner's first / last tile
+// row of level 1 — from the partner's shared memory (DSMEM) instead; the per-plane CTA barrier
+// becomes a cluster barrier.  Measured against the plain variant in profiles/cluster_variant.md.
+template <int TX, int RPT, int RG, int STAGES, int MINB = 1, int CLY = 1>
 struct PairCfg {
+  static constexpr int kClusterY = CLY;
   static constexpr int kMinBlocks = MINB;                  // CTAs per SM the launch bounds ask for
   static constexpr int kTX = TX, kRPT = RPT, kRG = RG, kStages = STAGES;
   static constexpr int kTY = RPT * RG;
@@ -142,8 +147,8 @@ __device__ __forceinline__ void pair_issue(const PairParams& P, uint64_t* full, 
 
 template <class Cfg, bool FULL, bool XFULL>
 __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* full, uint8_t* stage0,
-                                              double* l1buf, const double* s_sz, int x0, int y0, int yown, int z0, int z1,
-                                              double& mx1, double& s21, double& mx2, double& s22) {
+                                              double* l1buf, const double* s_sz, int x0, int y0, int yown, int cl_ov,
+                                              int z0, int z1, double& mx1, double& s21, double& mx2, double& s22) {
   constexpr int TX = Cfg::kTX, RPT = Cfg::kRPT, STAGES = Cfg::kStages;
   constexpr int WA = Cfg::kWA, WB = Cfg::kWB, W1 = Cfg::kW1;
   const TileGeom& T = P.tile;
@@ -193,8 +198,13 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
     else if (tid < 2 * W1) { rcx = tid - W1; rry = Cfg::kRows1 - 1; }
     else { const int q = tid - 2 * W1; rcx = (q & 1) ? W1 - 1 : 0; rry = 1 + (q >> 1); }
   }
+  // cluster variant: rank 0 owns the upper tile (smaller y) of the pair, rank 1 the lower one; the ring row
+  // facing the partner is not computed (its values are the partner's own tile row, read through DSMEM)
+  const uint32_t crank = Cfg::kClusterY == 2 ? cluster_ctarank() : 0u;
+  const bool ring_partner_row = Cfg::kClusterY == 2 && has_ring && tid < 2 * W1 &&
+                                (crank == 0 ? rry == Cfg::kRows1 - 1 : rry == 0);
   const int rgx = x0 - 1 + rcx, rgy = y0 - 1 + rry;
-  const bool ring_in = has_ring && rgx >= P.in_lo[0] && rgx <= P.in_hi[0] && rgy >= P.in_lo[1] && rgy <= P.in_hi[1];
+  const bool ring_in = has_ring && !ring_partner_row && rgx >= P.in_lo[0] && rgx <= P.in_hi[0] && rgy >= P.in_lo[1] && rgy <= P.in_hi[1];
   // wide halo: a ring node on the first ghost layer of x (or y) whose other coordinate is an
   // owned row (column) of this tile keeps its level-1 value in out1's ghost layer
   const bool ring_xg = rgx < 1 || rgx > g.n[0], ring_yg = rgy < 1 || rgy > g.n[1];
@@ -227,6 +237,14 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
   // finished in l1_phase(t)), szo = s_sz[t-2] (level-2 plane finished in l2_phase(t)).  A load at the
   // point of use exposed the shared-memory latency to every warp once per plane and level.
   double szc = 0.0, szo = 0.0, szn = 0.0;
+  // cluster variant: DSMEM addresses (buffer 0; buffer 1 is kL1Bytes further) of the level-1 value that
+  // sits above this thread's first row / below its last row when that row belongs to the partner
+  uint32_t ds_up = 0u, ds_dn = 0u;
+  if (Cfg::kClusterY == 2) {
+    // (cl_ov: rows by which the lower tile was moved back onto the upper one, see y0 in the kernel)
+    if (crank == 1 && r0 == 0) ds_up = dsmem_addr(l1buf + (Cfg::kTY - cl_ov) * W1 + cxi + 1, 0u);      // row y0-1 in the partner's plane
+    if (crank == 0 && r0 + RPT == Cfg::kTY) ds_dn = dsmem_addr(l1buf + (1 + cl_ov) * W1 + cxi + 1, 1u);  // row y0+TY in the partner's plane
+  }
 
   // The z pipeline of one plane is split in two phases.  zAp/zLp hold u^n / level 1 of the previous
   // plane (own column), zAc/zLc receive those of the current plane; the caller alternates the two
@@ -360,8 +378,15 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
       }
     }
     if (S || (p1 >= z0 && p1 < z1)) {
-      const double ym0 = L1w[off1 - W1];                 // row above this thread's rows
-      const double ypN = L1w[off1 + RPT * W1];           // row below
+      double ym0, ypN;                                   // rows above / below this thread's rows
+      if (Cfg::kClusterY == 2) {
+        const uint32_t par = (uint32_t)((t + 1) & 1) * (uint32_t)Cfg::kL1Bytes;
+        ym0 = ds_up ? ld_dsmem_f64(ds_up + par) : L1w[off1 - W1];
+        ypN = ds_dn ? ld_dsmem_f64(ds_dn + par) : L1w[off1 + RPT * W1];
+      } else {
+        ym0 = L1w[off1 - W1];
+        ypN = L1w[off1 + RPT * W1];
+      }
 #pragma unroll
       for (int r = 0; r < RPT; ++r) {
         const double xm = L1w[off1 + r * W1 - 1];
@@ -376,7 +401,9 @@ __device__ __forceinline__ void pair_consumer(const PairParams& P, uint64_t* ful
   };
   auto wait_stage = [&](const int t) { mbar_wait(full + t % STAGES, (uint32_t)(t / STAGES) & 1u); };
   auto sync_and_refill = [&](const int t) {
-    __syncthreads();          // level-1 plane p-1 is complete in smem AND every thread is done with stage t % STAGES
+    // level-1 plane p-1 is complete in smem AND every thread is done with stage t % STAGES
+    // (cluster variant: complete in BOTH CTAs of the pair, and the partner is done reading the plane before)
+    if (Cfg::kClusterY == 2) cluster_sync_all(); else __syncthreads();
     if (tid == 0 && t + STAGES < iters) pair_issue<Cfg>(P, full, stage0, t + STAGES, x0, y0, z0, nzc);
   };
   // General plane (any special case; a few planes at both ends of the chunk): ONE copy of the code, the
@@ -435,6 +462,11 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
   // slowest CTA sets the pass time, and the partial tiles were that CTA (mirrored in pair_tile_y0(), wave_api.cu).
   const int yown = T.lo[1] + ty * Cfg::kTY;
   const int y0 = (yown + Cfg::kTY > T.hi[1] && T.hi[1] - Cfg::kTY >= T.lo[1]) ? T.hi[1] - Cfg::kTY : yown;
+  int cl_ov = 0;      // cluster variant: overlap rows of the LOWER tile of the pair (known to both CTAs)
+  if (Cfg::kClusterY == 2) {
+    const int ylow = T.lo[1] + (ty | 1) * Cfg::kTY;     // nominal first row of the pair's lower tile (odd tile row)
+    cl_ov = (ylow + Cfg::kTY > T.hi[1] && T.hi[1] - Cfg::kTY >= T.lo[1]) ? ylow - (T.hi[1] - Cfg::kTY) : 0;
+  }
   const int z0 = T.lo[2] + ch * T.zc;
   const int z1 = min(z0 + T.zc, T.hi[2]);
   const int nzc = z1 - z0;
@@ -494,11 +526,12 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
     const bool xfull = x0 >= T.lo[0] && x0 >= 1 && x0 + TX <= T.hi[0] && !(P.skip_lo[0] && x0 <= 1) &&
                        !(P.skip_hi[0] && x0 + TX > g.n[0]);
     if (rows_full && xfull)
-      pair_consumer<Cfg, true, true>(P, full, stage0, l1buf, s_sz, x0, y0, yown, z0, z1, mx1, s21, mx2, s22);
+      pair_consumer<Cfg, true, true>(P, full, stage0, l1buf, s_sz, x0, y0, yown, cl_ov, z0, z1, mx1, s21, mx2, s22);
     else if (rows_full)
-      pair_consumer<Cfg, true, false>(P, full, stage0, l1buf, s_sz, x0, y0, yown, z0, z1, mx1, s21, mx2, s22);
+      pair_consumer<Cfg, true, false>(P, full, stage0, l1buf, s_sz, x0, y0, yown, cl_ov, z0, z1, mx1, s21, mx2, s22);
     else
-      pair_consumer<Cfg, false, false>(P, full, stage0, l1buf, s_sz, x0, y0, yown, z0, z1, mx1, s21, mx2, s22);
+      pair_consumer<Cfg, false, false>(P, full, stage0, l1buf, s_sz, x0, y0, yown, cl_ov, z0, z1, mx1, s21, mx2, s22);
+    if (Cfg::kClusterY == 2) cluster_sync_all();   // the partner may still be reading this CTA's level-1 planes
     if (mask) {
       __syncthreads();   // the tile's shipped level is written (CTA-visible), z-face pushes are issued
       const unsigned long long t_copy0 = P.xstat ? globaltimer_ns() : 0ull;

@@ -76,10 +76,12 @@ using PCfg9 = PairCfg<64, 3, 10, 3>;   // 640 threads, 3 rows per thread
 using PCfg10 = PairCfg<64, 6, 5, 4>;   // 320 threads, 6 rows per thread, 4-stage ring
 // (tried and dropped: 128 x 14 / 128 x 15 tiles — 4 x 37 = 148 / 4 x 35 = 140 CTAs at 511 x 511 — with 2 / 3
 // rows per thread: 0.085 / 0.072 ms per step on the 511 x 511 x 64 block against 0.057 for 64 x 32)
+using PCfg11 = PairCfg<64, 4, 8, 3, 1, 2>;  // the default tile in 2-CTA clusters along y (DSMEM ring rows, cluster barrier)
 struct PairVariant {
   int tx, ty, threads, smem, ctas_per_sm;
   void (*kernel)(const PairParams);
   const char* name;
+  int cluster_y;
 };
 const PairVariant kPairVariants[] = {
     {PCfg0::kTX, PCfg0::kTY, PCfg0::kThreads, PCfg0::kSmemBytes, 1, pair_step_kernel<PCfg0>, "pair 64x32x4st"},
@@ -93,6 +95,7 @@ const PairVariant kPairVariants[] = {
     {PCfg8::kTX, PCfg8::kTY, PCfg8::kThreads, PCfg8::kSmemBytes, 1, pair_step_kernel<PCfg8>, "pair 64x30x3st rpt5"},
     {PCfg9::kTX, PCfg9::kTY, PCfg9::kThreads, PCfg9::kSmemBytes, 1, pair_step_kernel<PCfg9>, "pair 64x30x3st rpt3"},
     {PCfg10::kTX, PCfg10::kTY, PCfg10::kThreads, PCfg10::kSmemBytes, 1, pair_step_kernel<PCfg10>, "pair 64x30x4st rpt6"},
+    {PCfg11::kTX, PCfg11::kTY, PCfg11::kThreads, PCfg11::kSmemBytes, 1, pair_step_kernel<PCfg11>, "pair 64x32x3st rpt4 cluster 1x2 (DSMEM)", 2},
 };
 constexpr int kNumPairVariants = sizeof(kPairVariants) / sizeof(kPairVariants[0]);
 constexpr int kDefaultVariant = 3;   // best of the measured sweep at 512^3 (profiles/variant_sweep.md)
@@ -673,15 +676,34 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const*
     // Wide halo: two layers are shipped, so both sets are the tiles within 2 layers of a face.
     const int depth = p->pair_mode == W3D_PAIR_WIDE ? 2 : 1;
     std::vector<int> face, waiters, rest;
-    for (int w = 0; w < p->pn_ctas; ++w) {
+    auto tile_class = [&](int w) {      // 2: copies halo layers out, 1: only waits, 0: neither
       const int tx = w % t.ntx, ty = (w / t.ntx) % t.nty, ch = w / (t.ntx * t.nty);
       const int lo[3] = {t.x0 + tx * v.tx, pair_tile_y0(t, ty, v.ty), t.lo[2] + ch * t.zc};
       const int hi[3] = {lo[0] + v.tx, lo[1] + v.ty, std::min(lo[2] + t.zc, t.hi[2])};
-      if (face_mask_host(p->d, p->g.n, lo, hi, depth)) face.push_back(w);
-      else if (face_mask_host(p->d, p->g.n, lo, hi, 2)) waiters.push_back(w);
-      else rest.push_back(w);
+      return face_mask_host(p->d, p->g.n, lo, hi, depth) ? 2 : face_mask_host(p->d, p->g.n, lo, hi, 2) ? 1 : 0;
+    };
+    int n_face = 0;
+    if (v.cluster_y == 2) {
+      // clusters are consecutive block indices: the two tiles of a y pair stay together (upper tile = rank 0)
+      if (t.nty % 2 != 0) return fail(W3D_EINVAL, "the cluster variant needs an even number of tile rows (have %d)", t.nty);
+      for (int ch = 0; ch < t.nchunks; ++ch)
+        for (int ty = 0; ty < t.nty; ty += 2)
+          for (int tx = 0; tx < t.ntx; ++tx) {
+            const int w0 = (ch * t.nty + ty) * t.ntx + tx, w1 = w0 + t.ntx;
+            const int c0 = tile_class(w0), c1 = tile_class(w1);
+            n_face += (c0 == 2) + (c1 == 2);
+            std::vector<int>& dst = std::max(c0, c1) == 2 ? face : std::max(c0, c1) == 1 ? waiters : rest;
+            dst.push_back(w0);
+            dst.push_back(w1);
+          }
+    } else {
+      for (int w = 0; w < p->pn_ctas; ++w) {
+        const int c = tile_class(w);
+        (c == 2 ? face : c == 1 ? waiters : rest).push_back(w);
+      }
+      n_face = (int)face.size();
     }
-    p->pn_face_ctas = (int)face.size();
+    p->pn_face_ctas = n_face;
     // A system fence + counter in every face CTA at the end of the pass costs 4.8 us when every CTA is a face
     // CTA (one-wave launches on thin slabs): the flags are published by the NEXT launch at its entry instead
     // (entry_release, kernels.cuh).
@@ -745,7 +767,7 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
   set_bcast(p, &P.err1, err1);
   set_bcast(p, &P.err2, err2);
   P.tile = p->ptile;
-  P.order = p->pn_face_ctas > 0 ? p->order_dev + W3D_MAX_PARTIALS : nullptr;   // identity when nothing to reorder
+  P.order = (p->pn_face_ctas > 0 || v.cluster_y == 2) ? p->order_dev + W3D_MAX_PARTIALS : nullptr;   // identity when nothing to reorder
   P.wide = wide ? 1 : 0;
   for (int d = 0; d < 3; ++d) {
     const int lo_act = p->d.peer[d * 2].active ? 1 : 0, hi_act = p->d.peer[d * 2 + 1].active ? 1 : 0;
@@ -783,8 +805,25 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
   P.timeout_ns = (unsigned long long)(p->d.spin_timeout_ms > 0 ? p->d.spin_timeout_ms : 10000) * 1000000ull;
   // (programmatic dependent launch was tried here: the graph's launch gap is 1.5 us and with one CTA per SM the
   // successor has nowhere to start early — no gain, profiles/pair_schedule.md)
-  v.kernel<<<p->pn_ctas, v.threads, v.smem, static_cast<cudaStream_t>(stream)>>>(P);
-  CUDA_TRY(cudaGetLastError());
+  if (v.cluster_y == 2) {
+    cudaLaunchConfig_t cfg;
+    std::memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)p->pn_ctas);
+    cfg.blockDim = dim3((unsigned)v.threads);
+    cfg.dynamicSmemBytes = (size_t)v.smem;
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, v.kernel, P));
+  } else {
+    v.kernel<<<p->pn_ctas, v.threads, v.smem, static_cast<cudaStream_t>(stream)>>>(P);
+    CUDA_TRY(cudaGetLastError());
+  }
   ++p->launches;
   return W3D_OK;
 }

@@ -447,3 +447,32 @@ def test_published_delta_on_L_pi(N, L, want):
     assert n == 20 and abs(l2 - want) <= 2e-6 * want
     omx, ol2 = analytic.oracle_errors(p, 20)
     assert abs(mx - omx) <= 5e-15 and abs(l2 - ol2) <= 1e-6 * ol2
+
+
+@pytest.mark.parametrize("N,bc,K", [((130, 65, 40), "ddd", 6), ((70, 100, 30), "ddp", 5), ((200, 129, 70), "ddd", 4),
+                                    ((65, 257, 24), "pdd", 4)])
+def test_cluster_variant_bit_exact(N, bc, K):
+    """2-CTA thread-block clusters along y: the ring row between the two tiles comes from the partner's
+    shared memory (DSMEM) after a cluster barrier instead of being recomputed.  Same bits as the CPU.
+
+    Sizes: an exact pair of tiles; four tile rows with the last one moved back by 29 rows (the DSMEM row
+    offsets depend on that overlap); several clusters; a periodic x axis (ghost column in a partial tile)."""
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem(N, 2.0, 1e-3, K, bc=bc)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=True, pair_variant=11)
+    assert "cluster" in s.describe()
+    res = s.run()
+    s.check_status()
+    ref, _, _ = _cpu_fields(p, K)
+    got = s.final_field().cpu().numpy()
+    assert np.array_equal(got, ref[K]), f"max diff {np.max(np.abs(got - ref[K]))}"
+    base, _ = cpu.solve(p, every=1)
+    for a, c in zip(res.trace, base):
+        assert a[2] == c[2] and abs(a[3] - c[3]) <= 1e-12 * c[3]
+
+
+def test_cluster_variant_needs_even_tile_rows():
+    from mpi_cuda_b200.ops.cuda import CudaLibError
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    with pytest.raises(CudaLibError, match="even number of tile rows"):
+        FusedSolver(WaveProblem((70, 70, 30), 2.0, 1e-3, 2), (1, 1, 1), _dev(), pair=True, pair_variant=11)
