@@ -29,8 +29,10 @@
 //    or different host threads without ordering) race on the array and give
 //    wrong results — order them yourself.
 //  * Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+//  * Errors are reported through the errbuf argument only; w3d_last_error() is not touched.
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <mutex>
@@ -135,8 +137,8 @@ int report(char* buf, size_t len, int code, const char* fmt, ...) {
 }
 
 constexpr int kMaxDevices = 64;
-std::mutex g_setup_mutex;
-unsigned char* g_scratch_ptr[kMaxDevices] = {};   // device address of the array, per device
+std::mutex g_setup_mutex;                                   // taken on a device's FIRST call only
+std::atomic<unsigned char*> g_scratch_ptr[kMaxDevices];     // device address of the array, per device (null = not resolved yet)
 
 }  // namespace
 
@@ -146,8 +148,10 @@ extern "C" int w3d_error_norms_noalloc(const double* u, const W3dBlock* blk, con
   if (errbuf && errbuf_len) errbuf[0] = '\0';
   if (!u || !blk || !sx || !sy || !sz || !out)
     return report(errbuf, errbuf_len, W3D_EINVAL, "w3d_error_norms_noalloc: null argument");
-  if (blk->n[0] < 1 || blk->n[1] < 1 || blk->n[2] < 1 || blk->pitch < blk->xoff + blk->n[0] + 2)
-    return report(errbuf, errbuf_len, W3D_EINVAL, "w3d_error_norms_noalloc: bad block layout");
+  if (blk->n[0] < 1 || blk->n[1] < 1 || blk->n[2] < 1 || blk->xoff < 0 || blk->pitch < blk->xoff + blk->n[0] + 2)
+    return report(errbuf, errbuf_len, W3D_EINVAL,
+                  "w3d_error_norms_noalloc: bad block layout (n = %d %d %d, xoff = %d, pitch = %lld; need n >= 1, "
+                  "xoff >= 0, pitch >= xoff + nx + 2)", blk->n[0], blk->n[1], blk->n[2], blk->xoff, (long long)blk->pitch);
   const long long rows = (long long)blk->n[1] * blk->n[2];
   if (rows > W3D_NOALLOC_MAX_ROWS)
     return report(errbuf, errbuf_len, W3D_ETOOBIG,
@@ -156,22 +160,27 @@ extern "C" int w3d_error_norms_noalloc(const double* u, const W3dBlock* blk, con
                   rows, W3D_NOALLOC_MAX_ROWS, W3D_NOALLOC_SCRATCH_BYTES);
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices)
-    return report(errbuf, errbuf_len, W3D_ECUDA, "w3d_error_norms_noalloc: cudaGetDevice: %s (device %d)",
-                  cudaGetErrorString(e), dev);
-  unsigned char* scratch = nullptr;
-  {
-    // once per device, with that device current: turn the symbol into a device address
+  if (e != cudaSuccess)
+    return report(errbuf, errbuf_len, W3D_ECUDA, "w3d_error_norms_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= kMaxDevices)
+    return report(errbuf, errbuf_len, W3D_EINVAL,
+                  "w3d_error_norms_noalloc: current device has index %d, this entry point keeps the scratch address "
+                  "of devices 0..%d only", dev, kMaxDevices - 1);
+  // Every call but the first on a device is one atomic load here.  The first one, with that device
+  // current, turns the symbol into a device address (under a mutex, so two first calls do not both do it).
+  unsigned char* scratch = g_scratch_ptr[dev].load(std::memory_order_acquire);
+  if (!scratch) {
     std::lock_guard<std::mutex> lock(g_setup_mutex);
-    if (!g_scratch_ptr[dev]) {
+    scratch = g_scratch_ptr[dev].load(std::memory_order_relaxed);
+    if (!scratch) {
       void* p = nullptr;
       e = cudaGetSymbolAddress(&p, w3d_noalloc_scratch);
       if (e != cudaSuccess || !p)
         return report(errbuf, errbuf_len, W3D_ECUDA, "w3d_error_norms_noalloc: cudaGetSymbolAddress: %s",
                       cudaGetErrorString(e));
-      g_scratch_ptr[dev] = static_cast<unsigned char*>(p);
+      scratch = static_cast<unsigned char*>(p);
+      g_scratch_ptr[dev].store(scratch, std::memory_order_release);
     }
-    scratch = g_scratch_ptr[dev];
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   // the ticket must start at zero whatever an earlier (possibly failed) call left there

@@ -11,8 +11,9 @@
  *   K6 error kernel + MPI_Reduce         -> epilogue of every step kernel; w3d_error_norms stand-alone
  *
  * All pointers are device pointers unless stated.  Every function returns 0 on
- * success or a negative W3D_E* code; w3d_last_error() gives the text.  Streams are
- * passed as void* (cudaStream_t).  No function synchronises the device.
+ * success or a negative W3D_E* code; w3d_last_error() gives the text (except for
+ * w3d_error_norms_noalloc, which writes it into its errbuf argument).  Streams are
+ * passed as void* (cudaStream_t).  No function synchronises the device unless it says so.
  */
 #ifndef WAVE3D_H
 #define WAVE3D_H

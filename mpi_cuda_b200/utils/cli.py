@@ -61,7 +61,7 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--bc", default="ddd", help="per-axis boundary: d (Dirichlet) or p (periodic), e.g. ddp")
     ap.add_argument("--backend", default="auto",
                     choices=("auto", "fused", "nccl", "gloo", "cpu", "cpu-omp", "cpu-ranks", "torch"))
-    ap.add_argument("--decomp", default="block", help="auto | slab | block | PxQxR")
+    ap.add_argument("--decomp", default="auto", help="auto (measured policy: z slabs) | slab | block | PxQxR")
     ap.add_argument("--ranks", type=int, default=1, help="in-process ranks for --backend cpu-ranks")
     ap.add_argument("--threads", type=int, default=None, help="OpenMP threads per rank")
     ap.add_argument("--report-every", type=int, default=2)
@@ -103,12 +103,16 @@ def _fused_session(p: WaveProblem, args, rank: int) -> int:
     p.check_cfl(strict=not args.no_cfl_check)
     world = dist.get_world_size() if dist.is_initialized() else 1
     s = FusedSolver(p, parse_dims(args.decomp, world, p.unknowns), every=args.report_every, variant=args.variant,
-                    zchunk=args.zchunk, use_graph=False)
+                    zchunk=args.zchunk, use_graph=False, pair=not args.no_pair)
     if args.trace:
         ms = s.profile_steps()
+        tl = s.device_timeline()           # %globaltimer stamps from inside the kernels: per-launch spans and gaps
+        xs = s.exchange_stats()
         if rank == 0:
-            write_chrome_trace(args.trace, ms, rank)
-            print(f"wrote {args.trace}: {len(ms)} steps, mean {sum(ms) / len(ms):.4f} ms/step")
+            write_chrome_trace(args.trace, ms, rank, device_spans=tl)
+            print(f"wrote {args.trace}: {len(ms)} steps, mean {sum(ms) / len(ms):.4f} ms/step; "
+                  f"{len(tl)} launches, in-kernel flag wait {xs['flag_wait_s'] * 1e6:.1f} us, "
+                  f"halo copy-out {xs['halo_copy_s'] * 1e6:.1f} us")
     else:
         first = 1
         if args.restart:

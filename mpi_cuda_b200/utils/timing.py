@@ -47,12 +47,18 @@ class PhaseTimer:
         return dict(self.totals)
 
 
-def write_chrome_trace(path: str, step_ms: List[float], rank: int = 0, name: str = "fused_step") -> None:
-    """step_ms[i] = device time of step i+1; written as back-to-back complete events."""
+def write_chrome_trace(path: str, step_ms: List[float], rank: int = 0, name: str = "fused_step",
+                       device_spans=None) -> None:
+    """step_ms[i] = device time of step i+1 (CUDA events); written as back-to-back complete events on
+    track 0.  ``device_spans`` = [(input level, start_us, end_us)] from ``FusedSolver.device_timeline``
+    (stamps taken inside the kernels) go on track 1: the distance between consecutive spans is the
+    launch gap, which event timing cannot see."""
     t = 0.0
     ev = []
     for i, ms in enumerate(step_ms):
         ev.append({"name": f"{name} {i + 1}", "ph": "X", "ts": t * 1e3, "dur": ms * 1e3, "pid": rank, "tid": 0})
         t += ms
+    for lv, b, e in (device_spans or []):
+        ev.append({"name": f"launch from level {lv}", "ph": "X", "ts": b, "dur": e - b, "pid": rank, "tid": 1})
     with open(path, "w") as fh:
         json.dump({"traceEvents": ev, "displayTimeUnit": "ms"}, fh)

@@ -327,6 +327,14 @@ def test_native_mpigpu_executable_matches_python_path():
     base, _ = cpu.solve(WaveProblem(96, 2.0, 1e-3, 10, bc="ddp"), every=2)
     got = [report.parse_step(l) for l in per.splitlines() if l.startswith("Step ")]
     assert len(got) == 5 and abs(got[-1][2] - base[-1][2]) <= 1e-6 * base[-1][2]
+    assert "wide halo" in per
+    # two periodic axes: fix-up protocol; odd K: the last step goes alone
+    per2 = subprocess.run([exe, "96", "0.001", "9", "--bc", "pdp", "--L", "2", "--every", "1"], capture_output=True, text=True, check=True).stdout
+    base2, _ = cpu.solve(WaveProblem(96, 2.0, 1e-3, 9, bc="pdp"), every=1)
+    got2 = [report.parse_step(l) for l in per2.splitlines() if l.startswith("Step ")]
+    assert "fix-up" in per2 and len(got2) == 9
+    for g, b in zip(got2, base2):
+        assert abs(g[2] - b[2]) <= 1e-6 * b[2] and abs(g[3] - b[3]) <= 1e-6 * b[3]
 
 
 @pytest.mark.parametrize("pair_variant", [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10])

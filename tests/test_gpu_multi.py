@@ -186,3 +186,26 @@ def test_native_mpigpu_two_gpus():
     b = [l for l in two.splitlines() if l.startswith("Step ")]
     assert len(a) == 10 and a == b          # digit-identical lines, like report.pdf p.15-16
     assert "and 2 processes" in two.splitlines()[0]
+    # block partition (report.pdf p.4 §1): split along y instead of z, and along x
+    for dims in (["1", "2", "1"], ["2", "1", "1"]):
+        blk = subprocess.run([exe, "--dims", *dims, "160", "0.001", "20"], capture_output=True, text=True, check=True).stdout
+        assert [l for l in blk.splitlines() if l.startswith("Step ")] == a
+    assert "exchange 0.000000" not in two       # the exchange column is measured, not a constant
+
+
+def test_native_mpigpu_blocks_four_and_eight_gpus():
+    """`mpigpu --dims P Q R`: 3-D blocks in the Python-free executable, digit-identical to one GPU."""
+    import os
+    import subprocess
+    n = torch.cuda.device_count()
+    if n < 4:
+        pytest.skip("needs 4 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "bin", "mpigpu")
+    one = subprocess.run([exe, "128", "0.001", "10", "--bc", "dpd", "--L", "2"], capture_output=True, text=True, check=True).stdout
+    a = [l for l in one.splitlines() if l.startswith("Step ")]
+    cases = [["1", "2", "2"], ["2", "2", "1"]] + ([["2", "2", "2"], ["1", "2", "4"], ["1", "1", "8"]] if n >= 8 else [])
+    for dims in cases:
+        out = subprocess.run([exe, "--dims", *dims, "128", "0.001", "10", "--bc", "dpd", "--L", "2"],
+                             capture_output=True, text=True, check=True).stdout
+        assert [l for l in out.splitlines() if l.startswith("Step ")] == a, dims

@@ -6,10 +6,12 @@ memory once from its own pool, or inside another solver's time loop where a
 and an output but no workspace, so the library keeps the scratch of the error
 reduction in a built-in 33 024-byte array per GPU.  This file checks, through the
 C ABI (ctypes, raw device pointers), that the result agrees with the regular
-``w3d_error_norms`` on two calls in a row (the second on a different, smaller
-field, so anything the first call left in the shared array would show), that an
-oversized block is refused with a readable message and leaves the output alone,
-and that the ticket is cleared even after it was left dirty.
+``w3d_error_norms`` on calls in a row — large field, small field, large field
+again — and that an oversized block is refused with a readable message and leaves
+the output alone.  The sequence is also the dirty-ticket case: every call leaves its
+CTA count in the array's ticket word, so the next call (fewer CTAs, then more) only
+finds its "last CTA" — and only then writes the output at all — if the entry point
+really clears the word first; the output is pre-filled with a sentinel to see that.
 
 Collected last on purpose (file name): a failure here cannot hide other tests
 from a run that stops at the first failure.  Needs a GPU.
@@ -56,16 +58,18 @@ def _call_c_abi(cuda, u, n, tabs, ct, out):
 
 
 def test_noalloc_matches_workspace_version_twice_in_a_row():
-    first, second = (150, 67, 45), (33, 20, 9)
+    first, second = (150, 67, 45), (33, 20, 9)            # 24 CTAs, then 2 CTAs, then 24 again
     cuda, dev, u1, t1 = _setup(first, 1)
     _, _, u2, t2 = _setup(second, 2)
     out = torch.full((2,), -1.0, dtype=torch.float64, device=dev)
     before = torch.cuda.memory_allocated(dev)
-    for n, u, tabs, ct in ((first, u1, t1, 0.75), (second, u2, t2, -0.3)):
+    for n, u, tabs, ct in ((first, u1, t1, 0.75), (second, u2, t2, -0.3), (first, u1, t1, 0.1)):
+        out.fill_(-1.0)                                    # sentinel: a call that never finds its last CTA leaves it
         rc, msg = _call_c_abi(cuda, u, n, tabs, ct, out)
         assert rc == 0, msg
         torch.cuda.synchronize()
         got = [float(v) for v in out.cpu()]
+        assert got[0] >= 0.0 and got[1] >= 0.0, "output not written: the ticket word was not cleared"
         want = _reference(cuda, dev, u, n, tabs, ct)
         assert got[0] == want[0]                               # max is order-independent
         assert abs(got[1] - want[1]) <= 1e-12 * want[1]        # sum: same tolerance as the other GPU tests
