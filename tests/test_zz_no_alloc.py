@@ -80,6 +80,7 @@ def test_noalloc_matches_workspace_version_twice_in_a_row():
         e = (core - exact).abs()
         assert abs(got[0] - float(e.max())) <= 1e-15 * max(1.0, got[0]) + 1e-15
         assert abs(got[1] - float((e * e).sum())) <= 1e-11 * got[1]
+    del core, exact, e, want
     assert torch.cuda.memory_allocated(dev) - before < (1 << 22)   # only the test's own small tensors
 
 
