@@ -532,6 +532,8 @@ int w3d_plan_set_timeline(W3dPlan* p, unsigned long long* dev_buf, int capacity)
   return W3D_OK;
 }
 
+int w3d_plan_pairs_enabled(W3dPlan* p) { return p && p->pair_ready ? 1 : 0; }
+
 int w3d_plan_pair_mode(W3dPlan* p) { return p ? p->pair_mode : W3D_PAIR_LOCAL; }
 
 int w3d_step_tma(W3dPlan* p, int s, double a, double b, double cscale, double ct, const int32_t lo[3],

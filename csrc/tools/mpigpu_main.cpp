@@ -80,7 +80,6 @@ struct Rank {
   void* ws = nullptr;
   double* trace = nullptr;     // (K+1) x 2 slots x (max, sum) on device
   W3dPlan* plan = nullptr;
-  int pair_mode = W3D_PAIR_LOCAL;
   std::vector<double> htrace;
   unsigned long long xstat[W3D_XSTAT_WORDS] = {0, 0, 0, 0, 0};
   float loop_ms = 0.f, init_ms = 0.f;
@@ -245,10 +244,7 @@ int main(int argc, char** argv) {
     d.flags_in = k.flags; d.status = k.status; d.workspace = k.ws; d.workspace_bytes = w3d_workspace_bytes();
     d.variant = o.variant; d.zchunk = o.zchunk; d.num_sms = 0; d.spin_timeout_ms = 0;
     W3(w3d_plan_create(&d, &k.plan));
-    if (pair) {
-      W3(w3d_plan_enable_pairs(k.plan, k.arr[2], k.arr[3], peer_aux, o.pair_variant, o.zchunk));
-      k.pair_mode = w3d_plan_pair_mode(k.plan);
-    }
+    if (pair) W3(w3d_plan_enable_pairs(k.plan, k.arr[2], k.arr[3], peer_aux, o.pair_variant, o.zchunk));
     if (o.verbose && r == 0) std::printf("plan (%d x %d x %d ranks): %s\n", o.dims[0], o.dims[1], o.dims[2], w3d_plan_describe(k.plan));
   }
   if (!pair && o.kernel != "fused") {
@@ -276,22 +272,19 @@ int main(int argc, char** argv) {
       CK(cudaStreamSynchronize(st));
       bar.wait();                          // flags are reset everywhere before anyone pushes
       CK(cudaEventRecord(e1, st));
-      double a1, b1, c1, a2, b2, c2;
+      double a1, b1, c1;
       if (pair) {
-        // array roles rotate over the four arrays: (0,1)->(2,3), (3,2)->(0,1), (1,0)->(2,3), ...; an odd K
-        // ends with one single step on whichever two arrays hold the last two levels
-        int n = 0, cur = 0, prev = 1;
-        while (n + 2 <= K) {
-          const int o1 = cur <= 1 ? 2 : 0, o2 = cur <= 1 ? 3 : 1;
-          coef_of(n + 1, &a1, &b1, &c1); coef_of(n + 2, &a2, &b2, &c2);
-          W3(w3d_step_pair(k.plan, n, cur, prev, o1, o2, a1, b1, c1, ct[n + 1], a2, b2, c2, ct[n + 2], slot(n + 1, 0), slot(n + 2, 0), st));
-          if (k.pair_mode == W3D_PAIR_FIXUP) W3(w3d_step_fixup(k.plan, n + 1, o1, cur, o2, a2, b2, c2, ct[n + 2], slot(n + 2, 1), st));
-          n += 2; cur = o2; prev = o1;
+        // the library's stepper picks the arrays: (0,1)->(2,3), (3,2)->(0,1), (1,0)->(2,3), ...; an odd K ends
+        // with one single step on whichever two arrays hold the last two levels
+        W3dStepper stp;
+        w3d_stepper_reset(&stp);
+        while (stp.level + 2 <= K) {
+          const int n = stp.level;
+          W3(w3d_advance_pair(k.plan, &stp, ct.data(), slot(n + 1, 0), slot(n + 2, 0), slot(n + 2, 1), st));
         }
-        if (n < K) {
-          coef_of(K, &a1, &b1, &c1);
+        if (stp.level < K) {
           if (K == 1) CK(cudaMemsetAsync(k.alloc[1], 0, (size_t)(k.n[2] + 2 + 2 * gs) * k.plane * sizeof(double), st));
-          W3(w3d_step_fused_on(k.plan, K - 1, cur, prev, a1, b1, c1, ct[K], slot(K, 0), st));
+          W3(w3d_advance_single(k.plan, &stp, ct.data(), slot(K, 0), st));
         }
       }
       for (int n = 1; n <= K && !pair; ++n) {

@@ -195,6 +195,50 @@ int w3d_plan_exchange_stats(W3dPlan* plan, unsigned long long out[W3D_XSTAT_WORD
  * launch's end and the next one's start is the launch gap that no event timing can see. */
 int w3d_plan_set_timeline(W3dPlan* plan, unsigned long long* dev_buf, int capacity);
 
+/* ---- time stepper ------------------------------------------------------------------------
+ * Which arrays hold the newest level and the one before, advanced by the library: the loop body of
+ * the reference's main() (report.pdf p.15 §4.2.4) without its copies.  ct is a HOST table of
+ * cos(a_t t_n), n = 0..K (ignored by the kernels while a device table is attached with
+ * w3d_plan_set_ct_table).  err pointers are device addresses of (max, sum) pairs or NULL.
+ * w3d_advance_pair: levels +1 and +2 in one pass (plus the fix-up launch when the plan needs it);
+ * w3d_advance_single: one level with the one-pass kernel (any plan; the last step of an odd-length
+ * run in pair plans). */
+typedef struct W3dStepper { int32_t level, cur, prev, reserved; } W3dStepper;
+void w3d_stepper_reset(W3dStepper* st);                       /* level 0 in array 0, nothing before it */
+int w3d_plan_pairs_enabled(W3dPlan* plan);                    /* 1 after w3d_plan_enable_pairs */
+int w3d_advance_pair(W3dPlan* plan, W3dStepper* st, const double* ct, double* err1, double* err2, double* err_fix,
+                     void* stream);
+int w3d_advance_single(W3dPlan* plan, W3dStepper* st, const double* ct, double* err, void* stream);
+
+/* ---- streaming session ------------------------------------------------------------------
+ * Step-by-step use with per-step host traffic, natively: w3d_session_step_async(n) copies step n's
+ * time factor from pinned host memory to the device (8 B), launches what can be launched (in pair
+ * plans the call for the second step of a pair launches the pass for both; the call for the first
+ * one only uploads), copies the error pairs of the finished levels back to pinned host memory and
+ * records an event; w3d_session_result(n) waits for that event only and folds the slots of step n
+ * into out[0] = max, out[1] = sum of squares (this rank).  Feed n = 1, 2, ... K in order; any number
+ * of steps may be in flight.  All buffers belong to the caller: ct_host (K+1 doubles) and err_host
+ * (K+1 rows of `slots` pairs) pinned, ct_dev (>= K+1 doubles) and err_dev (same shape as err_host:
+ * row n slot 0 = step kernels, slot 1 = fix-up pass) on the device.  The session attaches ct_dev to
+ * the plan (w3d_plan_set_ct_table) until it is destroyed.  Counterpart of the reference's per-step
+ * H2D/D2H traffic (report.pdf p.16 §4.4), reduced to 8 bytes in and 16*slots bytes out per step. */
+typedef struct W3dSession W3dSession;
+typedef struct W3dSessionDesc {
+  W3dPlan* plan;
+  int32_t K;
+  int32_t slots;
+  const double* ct_host;
+  double* ct_dev;
+  double* err_dev;
+  double* err_host;
+} W3dSessionDesc;
+int w3d_session_create(const W3dSessionDesc* desc, W3dSession** out);
+void w3d_session_destroy(W3dSession* s);
+int w3d_session_begin(W3dSession* s, const W3dStepper* st /* NULL = level 0 */);   /* after (re-)initialising the fields */
+int w3d_session_step_async(W3dSession* s, int n, void* stream);
+int w3d_session_result(W3dSession* s, int n, double out[2]);
+int w3d_session_stepper(W3dSession* s, W3dStepper* out);
+
 /* NCCL-baseline helpers (K5): contiguous face buffers of the unknowns of the two
  * other axes, fastest index first.  ghost=0 packs/unpacks the edge layer of
  * unknowns, ghost=1 the ghost layer. */

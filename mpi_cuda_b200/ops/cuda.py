@@ -39,6 +39,16 @@ class W3dPlanDesc(C.Structure):
                 ("n_err_peers", C.c_int32), ("ghost_depth", C.c_int32), ("plane_stride", C.c_int64)]
 
 
+class W3dStepper(C.Structure):
+    """Which arrays hold the newest level and the one before (include/wave3d.h)."""
+    _fields_ = [("level", C.c_int32), ("cur", C.c_int32), ("prev", C.c_int32), ("reserved", C.c_int32)]
+
+
+class W3dSessionDesc(C.Structure):
+    _fields_ = [("plan", C.c_void_p), ("K", C.c_int32), ("slots", C.c_int32), ("ct_host", C.c_void_p),
+                ("ct_dev", C.c_void_p), ("err_dev", C.c_void_p), ("err_host", C.c_void_p)]
+
+
 class CudaLibError(RuntimeError):
     pass
 
@@ -67,6 +77,18 @@ def lib() -> C.CDLL:
     l.w3d_step_fused.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
     l.w3d_step_fused_on.argtypes = [vp, C.c_int, C.c_int, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
     l.w3d_plan_pair_mode.argtypes = [vp]
+    l.w3d_plan_pairs_enabled.argtypes = [vp]
+    l.w3d_stepper_reset.argtypes = [C.POINTER(W3dStepper)]
+    l.w3d_stepper_reset.restype = None
+    l.w3d_advance_pair.argtypes = [vp, C.POINTER(W3dStepper), vp, vp, vp, vp, vp]
+    l.w3d_advance_single.argtypes = [vp, C.POINTER(W3dStepper), vp, vp, vp]
+    l.w3d_session_create.argtypes = [C.POINTER(W3dSessionDesc), C.POINTER(vp)]
+    l.w3d_session_destroy.argtypes = [vp]
+    l.w3d_session_destroy.restype = None
+    l.w3d_session_begin.argtypes = [vp, C.POINTER(W3dStepper)]
+    l.w3d_session_step_async.argtypes = [vp, C.c_int, vp]
+    l.w3d_session_result.argtypes = [vp, C.c_int, C.POINTER(C.c_double)]
+    l.w3d_session_stepper.argtypes = [vp, C.POINTER(W3dStepper)]
     l.w3d_plan_set_timeline.argtypes = [vp, vp, C.c_int]
     l.w3d_plan_exchange_stats.argtypes = [vp, C.POINTER(C.c_ulonglong), vp]
     l.w3d_step_tma.argtypes = [vp, C.c_int, dbl, dbl, dbl, dbl, i32p, i32p, vp, C.c_int, vp]
@@ -299,3 +321,51 @@ def error_norms(u: torch.Tensor, n: Sequence[int], tables: Sequence[torch.Tensor
     check(lib().w3d_error_norms(u.data_ptr(), C.byref(blk), tables[0].data_ptr(), tables[1].data_ptr(),
                                 tables[2].data_ptr(), ct, out.data_ptr(), workspace.data_ptr(),
                                 workspace.numel() * workspace.element_size(), stream_ptr()))
+
+
+class NativeSession:
+    """Thin handle on a W3dSession (csrc/cuda/session.cu): the per-step host work in native code."""
+
+    def __init__(self, plan: CudaPlan, K: int, slots: int, ct_host: torch.Tensor, ct_dev: torch.Tensor,
+                 err_dev: torch.Tensor, err_host: torch.Tensor):
+        assert ct_host.is_pinned() and err_host.is_pinned() and ct_dev.is_cuda and err_dev.is_cuda
+        assert err_dev.is_contiguous() and err_host.is_contiguous() and err_dev.numel() == err_host.numel()
+        self._keep = (plan, ct_host, ct_dev, err_dev, err_host)      # the session only borrows these
+        d = W3dSessionDesc()
+        d.plan, d.K, d.slots = plan._h, K, slots
+        d.ct_host, d.ct_dev = ct_host.data_ptr(), ct_dev.data_ptr()
+        d.err_dev, d.err_host = err_dev.data_ptr(), err_host.data_ptr()
+        h = C.c_void_p()
+        check(lib().w3d_session_create(C.byref(d), C.byref(h)))
+        self._h = h
+        self._out = (C.c_double * 2)()
+        self._step, self._result = lib().w3d_session_step_async, lib().w3d_session_result
+
+    def close(self) -> None:
+        if self._h:
+            lib().w3d_session_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def begin(self, level: int = 0, cur: int = 0, prev: int = 1) -> None:
+        st = W3dStepper(level, cur, prev, 0)
+        check(lib().w3d_session_begin(self._h, C.byref(st)))
+
+    def step_async(self, n: int, stream: int) -> None:
+        rc = self._step(self._h, n, stream)
+        if rc != 0:
+            raise CudaLibError(f"w3d_session_step_async({n}) failed ({rc}): feed consecutive steps 1..K; "
+                               f"{lib().w3d_last_error().decode()}")
+
+    def result(self, n: int) -> Tuple[float, float]:
+        rc = self._result(self._h, n, self._out)
+        if rc != 0:
+            raise CudaLibError(f"w3d_session_result({n}) failed ({rc}): step not launched yet "
+                               "(pair plans launch two steps at a time)")
+        return self._out[0], self._out[1]
+
+    def stepper(self) -> Tuple[int, int, int]:
+        st = W3dStepper()
+        check(lib().w3d_session_stepper(self._h, C.byref(st)))
+        return st.level, st.cur, st.prev

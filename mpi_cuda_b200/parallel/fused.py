@@ -478,17 +478,24 @@ class StreamingSession:
         self.ct_host = torch.from_numpy(solver.ct.copy()).pin_memory()
         self.ct_dev = torch.zeros(p.K + 2, dtype=torch.float64, device=solver.device)
         self.err_host = torch.zeros((p.K + 1, _SLOTS, 2), dtype=torch.float64).pin_memory()
-        self._err_np = self.err_host.numpy()             # same memory: reading a result costs no torch dispatch
-        # per-step views made once (slicing a tensor costs more than the 8-byte copy it feeds)
-        self._ct_src = [self.ct_host[n: n + 1] for n in range(p.K + 1)]
-        self._ct_dst = [self.ct_dev[n: n + 1] for n in range(p.K + 1)]
-        self._done: Dict[int, torch.cuda.Event] = {}
         self.tab_host = [torch.from_numpy(t).pin_memory()
                          for t in local_tables(p, solver.blk, ghosts=2 if solver.pair else 1)]
-        solver.plan.set_ct_table(self.ct_dev)
+        # The per-step host work (8-byte upload, choice of arrays, launch, read-back, event) runs in native
+        # code (csrc/cuda/session.cu): a pass is 105 us at 512^3 on eight GPUs, an interpreter is slower.
+        self.native = cuda.NativeSession(solver.plan, p.K, _SLOTS, self.ct_host, self.ct_dev,
+                                         solver.table[solver.rank], self.err_host)
 
     def close(self) -> None:
-        self.s.plan.set_ct_table(None)
+        """Detach from the plan; the solver takes over where the session stopped."""
+        if self.native is not None:
+            self._sync_solver()
+            self.native.close()
+            self.native = None
+
+    def _sync_solver(self) -> None:
+        s = self.s
+        s.level, s._cur, s._prev = self.native.stepper()
+        s.final_index = s._cur
 
     def start(self) -> None:
         """Upload the analytic tables from pinned host memory and build layer 0."""
@@ -496,6 +503,8 @@ class StreamingSession:
         for dst, src in zip(s.tab_full, self.tab_host):
             dst.copy_(src, non_blocking=True)
         s.init(host_sync=False)
+        self.native.begin(0, 0, 1)
+        self._stream = cuda.stream_ptr()
 
     @property
     def table_bytes(self) -> int:
@@ -507,35 +516,11 @@ class StreamingSession:
         In pair mode two steps travel together: the call for the first step of a pair only
         uploads its input, the call for the second one launches the pass and reads both back;
         the last step of an odd-length run goes alone."""
-        s = self.s
-        self._ct_dst[n].copy_(self._ct_src[n], non_blocking=True)
-        if s.pair:
-            if n == s.level + 2:
-                s.pair_advance(s.level, force_err=True)
-                self._finish(n - 1, n)
-            elif n == s.level + 1 and n == s.p.K:
-                s.step(n, True)
-                self._finish(n, n)
-            elif n != s.level + 1:
-                raise RuntimeError(f"step_async({n}): the solver holds level {s.level}; feed consecutive steps")
-            return
-        s.step(n, True)
-        self._finish(n, n)
-
-    def _finish(self, first: int, last: int) -> None:
-        self.err_host[first: last + 1].copy_(self.s.table[self.s.rank, first: last + 1], non_blocking=True)
-        ev = torch.cuda.Event()
-        ev.record()
-        for n in range(first, last + 1):
-            self._done[n] = ev
+        self.native.step_async(n, self._stream)
 
     def result(self, n: int) -> Tuple[float, float]:
         """(max error, sum of squares) of step n on this rank; waits for its read-back only."""
-        if n not in self._done:
-            raise RuntimeError(f"step {n} has not been launched yet (pair mode launches two steps at a time)")
-        self._done.pop(n).synchronize()
-        e = self._err_np[n]
-        return max(float(e[0, 0]), float(e[1, 0])), float(e[0, 1]) + float(e[1, 1])
+        return self.native.result(n)
 
     def step(self, n: int) -> Tuple[float, float]:
         """Synchronous single step (not available in pair mode, where steps come in twos)."""
