@@ -39,9 +39,6 @@
 #pragma once
 #include "kernels.cuh"
 
-#ifndef W3D_PAIR_THREAD_DISPATCH
-#define W3D_PAIR_THREAD_DISPATCH 0
-#endif
 
 namespace w3d {
 
@@ -510,17 +507,12 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
   }
   __syncthreads();
   {
-    // Fast paths are chosen per THREAD GROUP (the TX threads that share a set of rows = whole warps):
-    // FULL: all rows of this thread are owned, updated and free of skipped rows; XFULL: the tile is
-    // complete in x and free of skipped columns.  In a tile that is only partial in y just the
-    // row group that holds the dead rows pays for predicates — in a one-wave launch the slowest
-    // CTA sets the pass time, and before this split every CTA of the last tile row was that CTA.
-    // (All instantiations have the same barrier structure: one CTA barrier per plane.)
-#if W3D_PAIR_THREAD_DISPATCH
-    const int gy0 = y0 + (threadIdx.x / TX) * Cfg::kRPT, gy1 = gy0 + Cfg::kRPT;
-#else
+    // Fast paths, chosen per tile (one code path per CTA).  FULL: every row of the tile is owned, updated and
+    // free of skipped rows — true for every tile row now that a last partial row is moved back (y0 above),
+    // except in blocks thinner than a tile and next to a skipped face of the fix-up protocol; XFULL: the tile is
+    // complete in x and free of skipped columns.  All instantiations have the same barrier structure.
+    // (A choice per thread group was measured slower: three code paths live in one CTA, profiles/pair_schedule.md.)
     const int gy0 = y0, gy1 = y0 + Cfg::kTY;       // whole tile: one code path per CTA
-#endif
     const bool rows_full = gy0 >= T.lo[1] && gy1 <= T.hi[1] && !(P.skip_lo[1] && gy0 <= 1) &&
                            !(P.skip_hi[1] && gy1 > g.n[1]);
     const bool xfull = x0 >= T.lo[0] && x0 >= 1 && x0 + TX <= T.hi[0] && !(P.skip_lo[0] && x0 <= 1) &&
