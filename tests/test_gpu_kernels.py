@@ -484,3 +484,21 @@ def test_cluster_variant_needs_even_tile_rows():
     from mpi_cuda_b200.parallel.fused import FusedSolver
     with pytest.raises(CudaLibError, match="even number of tile rows"):
         FusedSolver(WaveProblem((70, 70, 30), 2.0, 1e-3, 2), (1, 1, 1), _dev(), pair=True, pair_variant=11)
+
+
+def test_north_star_1024_L_pi_K100_matches_oracle():
+    """1024^3 on [0,pi]^3, K = 100 (the CFL-stable north-star configuration; SURVEY.md App. A.4:
+    Max 7.975469e-09, L2 2.823890e-09 at step 100) on ONE GPU: 4 x 8.7 GB arrays, 0.3 s of stepping."""
+    from mpi_cuda_b200.parallel.fused import FusedSolver
+    p = WaveProblem(1024, math.pi, 1e-3, 100)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=10, use_graph=True)
+    res = s.run()
+    s.check_status()
+    assert len(res.trace) == 10
+    for n, t, mx, l2 in res.trace:
+        omx, ol2 = analytic.oracle_errors(p, n)
+        assert abs(mx - omx) <= 5e-15 * max(1.0, n / 20.0) and abs(l2 - ol2) <= 1e-6 * ol2
+    n, t, mx, l2 = res.trace[-1]
+    assert n == 100 and abs(mx - 7.975469e-09) <= 3e-14 and abs(l2 - 2.823890e-09) <= 3e-15
+    del s
+    torch.cuda.empty_cache()
