@@ -65,6 +65,27 @@ struct PeerDev {
   unsigned long long* flag;
 };
 
+// Wide halo on 3-D blocks: the two-step stencil also reaches the diagonal neighbours across an edge
+// (level 1 on the ghost layer of face a next to face b reads u^n on the edge line between them).
+// Edge e = 4 * pair + 2 * sa + sb, pair 0 = (x,y), 1 = (x,z), 2 = (y,z); sa, sb = my sides (0 low, 1 high).
+// My edge line (edge layer of both axes, all owned nodes of the third) fills the diagonal
+// neighbour's ghost line (ga, gb); its incoming flag word for that edge is `flag`.
+constexpr int kEdges = 12;
+struct EdgeDev {
+  int active;
+  int ga, gb;
+  double* field;          // the diagonal neighbour's array that holds the level being shipped
+  long long pitch, plane;
+  unsigned long long* flag;
+};
+__host__ __device__ __forceinline__ void edge_axes(int e, int* a, int* b, int* sa, int* sb) {
+  const int pair = e >> 2;
+  *a = pair == 2 ? 1 : 0;
+  *b = pair == 0 ? 1 : 2;
+  *sa = (e >> 1) & 1;
+  *sb = e & 1;
+}
+
 struct BoxTable {
   int nboxes;
   int lo[kMaxBoxes][3];
@@ -111,7 +132,8 @@ struct alignas(64) StepParams {
   const int* order;       // block index -> tile index (face CTAs first), nullptr = identity
   int use_flags;
   PeerDev peer[6];
-  const unsigned long long* flags_in;
+  EdgeDev edge[kEdges];            // wide-halo plans on 3-D blocks only (all inactive otherwise)
+  const unsigned long long* flags_in;   // 6 face words, then 12 edge words
   unsigned* shell_counter;
   unsigned* status;
   XStat* xstat;
@@ -374,6 +396,21 @@ __device__ __noinline__ unsigned long long wait_peer_flags(const PT& P, int mask
       }
     }
   }
+  // edge lines of the diagonal neighbours: needed by a tile that reads the ghost layers of both faces
+  for (int e = 0; e < kEdges; ++e) {
+    if (!P.edge[e].active) continue;
+    int a, b, sa, sb;
+    edge_axes(e, &a, &b, &sa, &sb);
+    if (!(mask & (1 << (a * 2 + sa))) || !(mask & (1 << (b * 2 + sb)))) continue;
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned spins = 0;
+    while (ld_acquire_sys(P.flags_in + 6 + e) < P.level) {
+      if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > P.timeout_ns) {
+        atomicExch(P.status, 0x200u + (unsigned)e);
+        break;
+      }
+    }
+  }
   fence_proxy_async_global();
   return globaltimer_ns() - t_in;
 }
@@ -398,6 +435,8 @@ __device__ __noinline__ void face_cta_done(const PT& P, unsigned long long wait_
     __threadfence_system();
     for (int f = 0; f < 6; ++f)
       if (P.peer[f].active) st_release_sys(P.peer[f].flag, P.release);
+    for (int e = 0; e < kEdges; ++e)
+      if (P.edge[e].active) st_release_sys(P.edge[e].flag, P.release);
     if (P.xstat) {
       xstat_fold(P.xstat, slot);
       if (!P.defer_release) P.xstat->launches += 1ull;     // (deferred plans count at kernel entry)
@@ -417,6 +456,8 @@ __device__ __noinline__ void entry_release(const PT& P) {
   __threadfence_system();                        // ONE system-scope fence, then relaxed stores = release pattern
   for (int f = 0; f < 6; ++f)
     if (P.peer[f].active) st_relaxed_sys(P.peer[f].flag, P.level);
+  for (int e = 0; e < kEdges; ++e)
+    if (P.edge[e].active) st_relaxed_sys(P.edge[e].flag, P.level);
   if (P.xstat) {
     xstat_fold(P.xstat, (P.seq & 1) ^ 1);      // the previous launch's maxima
     P.xstat->launches += 1ull;
@@ -517,6 +558,34 @@ __device__ __noinline__ void face_copy_out(const PT& P, int mask, int x0, int y0
 #pragma unroll
       for (int u = 0; u < 4; ++u)
         if (base + u * nthreads < total) pr.field[dst[u]] = v[u];   // peer-mapped: goes over NVLink
+    }
+  }
+}
+
+// Edge lines (wide halo on 3-D blocks): a tile that owns nodes of the line where the edge layers of
+// two faces with neighbours meet copies them into the diagonal neighbour's ghost line.
+template <class PT>
+__device__ __noinline__ void edge_copy_out(const PT& P, int x0, int y0, int z0, int z1, int tx_w, int ty_w, int tid,
+                                           int nthreads) {
+  const Geometry& g = P.g;
+  const TileGeom& T = P.tile;
+  const int tlo[3] = {max(x0, T.lo[0]), max(y0, T.lo[1]), z0};
+  const int thi[3] = {min(x0 + tx_w, T.hi[0]), min(y0 + ty_w, T.hi[1]), z1};
+#pragma unroll 1
+  for (int e = 0; e < kEdges; ++e) {
+    const EdgeDev& ed = P.edge[e];
+    if (!ed.active) continue;
+    int a, b, sa, sb;
+    edge_axes(e, &a, &b, &sa, &sb);
+    const int c = 3 - a - b;
+    const int la = sa ? g.n[a] : 1, lb = sb ? g.n[b] : 1;
+    if (la < tlo[a] || la >= thi[a] || lb < tlo[b] || lb >= thi[b]) continue;
+    for (int i = tlo[c] + tid; i < thi[c]; i += nthreads) {
+      int q[3];
+      q[a] = la; q[b] = lb; q[c] = i;
+      const double v = __ldcg(P.nxt + gidx(g, q[0], q[1], q[2]));
+      q[a] = ed.ga; q[b] = ed.gb;
+      ed.field[(long long)q[2] * ed.plane + (long long)q[1] * ed.pitch + g.xoff + q[0]] = v;   // peer-mapped: NVLink
     }
   }
 }
@@ -641,7 +710,10 @@ __device__ __forceinline__ void tma_role(const StepParams& P, int x0, int y0, in
   if (mask) {
     named_bar_sync(kConsBarrier, Cfg::kConsumers);   // the tile is written (CTA-visible)
     const unsigned long long t_copy0 = P.xstat ? globaltimer_ns() : 0ull;
-    if (!W3D_DIAG_SKIP(P, 2)) face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kConsumers);
+    if (!W3D_DIAG_SKIP(P, 2)) {
+      face_copy_out(P, mask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kConsumers);
+      edge_copy_out(P, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kConsumers);
+    }
     named_bar_sync(kConsBarrier, Cfg::kConsumers);   // every consumer's peer stores are issued
     if (threadIdx.x == 0 && !W3D_DIAG_SKIP(P, 4))
       face_cta_done(P, *reinterpret_cast<volatile unsigned long long*>(smem + 128 + 1016), t_copy0);

@@ -97,6 +97,7 @@ struct alignas(64) PairParams {
   int n_face_ctas;
   int use_flags;
   PeerDev peer[6];
+  EdgeDev edge[kEdges];   // wide halo on 3-D blocks: the diagonal neighbours across the edges (all inactive otherwise)
   const unsigned long long* flags_in;
   unsigned* shell_counter;
   unsigned* status;
@@ -530,6 +531,7 @@ __global__ void __launch_bounds__(Cfg::kThreads, Cfg::kMinBlocks) pair_step_kern
       const int cmask = mask & ~((P.zpush & 1 ? 16 : 0) | (P.zpush & 2 ? 32 : 0));   // faces still to copy: x, y
       if (cmask) {
         face_copy_out(P, cmask, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kThreads);
+        edge_copy_out(P, x0, y0, z0, z1, TX, Cfg::kTY, threadIdx.x, Cfg::kThreads);   // (every edge has a face in cmask)
         __syncthreads();
       }
       if (threadIdx.x == 0) {

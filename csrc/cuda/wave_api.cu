@@ -152,6 +152,8 @@ struct W3dPlan {
   bool pair_ready;
   int pair_mode;                   // W3D_PAIR_LOCAL / WIDE / FIXUP
   int step_depth;                  // halo layers the single-step kernel ships: 1, or 2 in wide-halo plans
+  W3dEdgePeer edges[W3D_EDGES];    // diagonal neighbours across the edges (wide halo on 3-D blocks)
+  bool have_edges;
   bool defer;                      // wide halo, (nearly) all pair CTAs are face CTAs: flags are published at the next launch's entry
   int launch_seq;                  // launches issued through this plan (parity selects the XStat slot)
   unsigned long long* timeline;    // optional device buffer of (start, end) stamps per launch, indexed by level
@@ -245,6 +247,20 @@ void plan_tiles(const W3dPlan* p, const int lo[3], const int hi[3], int zchunk, 
 int pair_tile_y0(const TileGeom& t, int ty, int tile_y) {
   const int y = t.lo[1] + ty * tile_y;
   return (y + tile_y > t.hi[1] && t.hi[1] - tile_y >= t.lo[1]) ? t.hi[1] - tile_y : y;
+}
+
+// the diagonal neighbours' array `ship` as kernel parameters (wide-halo plans on 3-D blocks)
+void fill_edges(const W3dPlan* p, EdgeDev* out, int ship) {
+  for (int e = 0; e < kEdges; ++e) {
+    const W3dEdgePeer& q = p->edges[e];
+    out[e].active = (p->pair_mode == W3D_PAIR_WIDE && q.active) ? 1 : 0;
+    out[e].ga = q.ghost_a;
+    out[e].gb = q.ghost_b;
+    out[e].field = q.arr[ship];
+    out[e].pitch = q.pitch;
+    out[e].plane = q.plane;
+    out[e].flag = q.flag;
+  }
 }
 
 // host mirror of tile_face_mask() (kernels.cuh)
@@ -381,6 +397,8 @@ int w3d_plan_create(const W3dPlanDesc* desc, W3dPlan** out) {
   p->timeline_cap = 0;
   p->launch_seq = 0;
   p->defer = false;
+  p->have_edges = false;
+  std::memset(p->edges, 0, sizeof(p->edges));
   p->variant = desc->variant >= 0 && desc->variant < kNumVariants ? desc->variant : kDefaultVariant;
   p->num_sms = desc->num_sms;
   if (p->num_sms <= 0) {
@@ -461,7 +479,7 @@ int w3d_plan_init_ex(W3dPlan* p, void* stream, int zero_second) {
                                       p->d.tab[1], p->d.tab[2]);
   CUDA_TRY(cudaGetLastError());
   ++p->launches;
-  CUDA_TRY(cudaMemsetAsync(p->d.flags_in, 0, 6 * sizeof(unsigned long long), st));
+  CUDA_TRY(cudaMemsetAsync(p->d.flags_in, 0, (p->have_edges ? W3D_FLAG_WORDS : 6) * sizeof(unsigned long long), st));
   CUDA_TRY(cudaMemsetAsync(p->d.status, 0, sizeof(uint32_t), st));
   CUDA_TRY(cudaMemsetAsync(p->d.workspace, 0, kCounterBytes, st));
   return W3D_OK;
@@ -490,6 +508,7 @@ static int step_fused_impl(W3dPlan* p, int s, int cur, int nxt, double a, double
     P.peer[f].plane = q.plane;
     P.peer[f].flag = q.flag;
   }
+  fill_edges(p, P.edge, nxt);
 #ifdef W3D_DIAG
   if (const char* dbg = std::getenv("W3D_DEBUG_SKIP")) P.debug_skip = std::atoi(dbg);   // timing diagnostics, wrong results
 #endif
@@ -529,6 +548,22 @@ int w3d_plan_set_timeline(W3dPlan* p, unsigned long long* dev_buf, int capacity)
   if (!p) return fail(W3D_EINVAL, "null plan");
   p->timeline = dev_buf;
   p->timeline_cap = dev_buf ? capacity : 0;
+  return W3D_OK;
+}
+
+int w3d_plan_set_edges(W3dPlan* p, const W3dEdgePeer* edges) {
+  if (!p) return fail(W3D_EINVAL, "null plan");
+  if (p->pair_ready) return fail(W3D_EINVAL, "w3d_plan_set_edges must come before w3d_plan_enable_pairs");
+  std::memset(p->edges, 0, sizeof(p->edges));
+  p->have_edges = false;
+  if (!edges) return W3D_OK;
+  for (int e = 0; e < W3D_EDGES; ++e) {
+    if (!edges[e].active) continue;
+    if (!edges[e].flag || !edges[e].arr[0] || !edges[e].arr[1] || !edges[e].arr[2] || !edges[e].arr[3])
+      return fail(W3D_EINVAL, "edge %d is active but has a null array or flag pointer", e);
+    p->edges[e] = edges[e];
+    p->have_edges = true;
+  }
   return W3D_OK;
 }
 
@@ -635,7 +670,15 @@ int w3d_plan_enable_pairs(W3dPlan* p, double* aux0, double* aux1, double* const*
   // protocol for faces with a neighbour (see wave3d.h)
   int active_axes = 0;
   for (int d = 0; d < 3; ++d) active_axes += (p->d.peer[d * 2].active || p->d.peer[d * 2 + 1].active) ? 1 : 0;
-  p->pair_mode = active_axes == 0 ? W3D_PAIR_LOCAL : (p->g.gs == 1 && active_axes == 1) ? W3D_PAIR_WIDE : W3D_PAIR_FIXUP;
+  // wide halo needs two ghost layers and, wherever two faces on different axes both have a neighbour, the rank
+  // diagonally across that edge (w3d_plan_set_edges)
+  bool edges_ok = true;
+  for (int e = 0; e < kEdges; ++e) {
+    int a, b, sa, sb;
+    edge_axes(e, &a, &b, &sa, &sb);
+    if (p->d.peer[a * 2 + sa].active && p->d.peer[b * 2 + sb].active && !p->edges[e].active) edges_ok = false;
+  }
+  p->pair_mode = active_axes == 0 ? W3D_PAIR_LOCAL : (p->g.gs == 1 && (active_axes == 1 || edges_ok)) ? W3D_PAIR_WIDE : W3D_PAIR_FIXUP;
   if (p->pair_mode == W3D_PAIR_WIDE)
     for (int d = 0; d < 3; ++d)
       if ((p->d.peer[d * 2].active || p->d.peer[d * 2 + 1].active) && p->g.n[d] < 2)
@@ -795,6 +838,7 @@ int w3d_step_pair(W3dPlan* p, int s, int cur, int prev, int out1, int out2, doub
     P.peer[f].plane = q.plane;
     P.peer[f].flag = q.flag;
   }
+  fill_edges(p, P.edge, ship);
   P.flags_in = p->d.flags_in;
   P.shell_counter = reinterpret_cast<unsigned*>(static_cast<char*>(p->d.workspace) + 64);
   P.status = p->d.status;

@@ -8,12 +8,12 @@
 // MPI in this program.
 //
 //   mpigpu [-np G] [--dims P Q R] N tau K [threads] [--L L | --Lpi] [--bc ddd] [--variant v]
-//          [--pair-variant v] [--zchunk z] [--every n] [--quiet] [--kernel pair|fused|tma|box]
+//          [--pair-variant v] [--zchunk z] [--every n] [--quiet] [--kernel pair|fused|tma|box] [--fixup]
 //
 // -np G alone: z slabs (1 x 1 x G).  --dims P Q R: a P x Q x R grid of blocks (x, y, z), P*Q*R GPUs.
 // --kernel pair (default): two time steps per pass on arrays with two ghost layers — one launch
-// and one halo handshake per two steps when one axis has neighbours (wide halo), pair + fix-up
-// launches otherwise; fused: one pass per step.
+// and one halo handshake per two steps (wide halo; on 3-D blocks the edge lines go to the diagonal
+// neighbours as well); --fixup: pair + fix-up launches on 3-D blocks instead; fused: one pass per step.
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -49,7 +49,7 @@
   } while (0)
 
 struct Opts {
-  int N = 512, K = 20, G = 1, variant = -1, pair_variant = -1, zchunk = 0, every = 2, verbose = 1;
+  int N = 512, K = 20, G = 1, variant = -1, pair_variant = -1, zchunk = 0, every = 2, verbose = 1, no_edges = 0;
   int dims[3] = {0, 0, 0};
   double tau = 1e-3, L = 1.0;
   int periodic[3] = {0, 0, 0};
@@ -108,6 +108,7 @@ int main(int argc, char** argv) {
     else if (a == "--every") o.every = std::atoi(nxt());
     else if (a == "--kernel") o.kernel = nxt();
     else if (a == "--quiet") o.verbose = 0;
+    else if (a == "--fixup") o.no_edges = 1;       // 3-D blocks: fix-up protocol instead of the wide halo with edge lines
     else pos.push_back(a);
   }
   if (pos.size() < 3) {
@@ -178,7 +179,7 @@ int main(int argc, char** argv) {
       CK(cudaMemset(k.alloc[f], 0, elems * sizeof(double)));
       k.arr[f] = k.alloc[f] + (size_t)gs * (k.plane + k.blk.pitch);
     }
-    CK(cudaMalloc(&k.flags, 64)); CK(cudaMemset(k.flags, 0, 64));
+    CK(cudaMalloc(&k.flags, 256)); CK(cudaMemset(k.flags, 0, 256));     // 6 face + 12 edge flag words
     CK(cudaMalloc(&k.status, 16)); CK(cudaMemset(k.status, 0, 16));
     CK(cudaMalloc(&k.ws, w3d_workspace_bytes())); CK(cudaMemset(k.ws, 0, w3d_workspace_bytes()));
     CK(cudaMalloc(&k.trace, sizeof(double) * 4 * (K + 1))); CK(cudaMemset(k.trace, 0, sizeof(double) * 4 * (K + 1)));   // 2 slots x (max, sum)
@@ -244,7 +245,31 @@ int main(int argc, char** argv) {
     d.flags_in = k.flags; d.status = k.status; d.workspace = k.ws; d.workspace_bytes = w3d_workspace_bytes();
     d.variant = o.variant; d.zchunk = o.zchunk; d.num_sms = 0; d.spin_timeout_ms = 0;
     W3(w3d_plan_create(&d, &k.plan));
-    if (pair) W3(w3d_plan_enable_pairs(k.plan, k.arr[2], k.arr[3], peer_aux, o.pair_variant, o.zchunk));
+    if (pair) {
+      // 3-D blocks: the ranks diagonally across the block's edges (neighbour of the neighbour), so that two
+      // steps share one launch and one handshake there too
+      W3dEdgePeer edges[W3D_EDGES];
+      std::memset(edges, 0, sizeof(edges));
+      static const int kPairs[3][2] = {{0, 1}, {0, 2}, {1, 2}};
+      bool any = false;
+      for (int pi = 0; pi < 3; ++pi)
+        for (int sa = 0; sa < 2; ++sa)
+          for (int sb = 0; sb < 2; ++sb) {
+            const int a = kPairs[pi][0], b = kPairs[pi][1];
+            if (k.nbr[a][sa] < 0 || k.nbr[b][sb] < 0) continue;
+            const Rank& D = R[R[k.nbr[a][sa]].nbr[b][sb]];
+            W3dEdgePeer& e = edges[4 * pi + 2 * sa + sb];
+            e.active = 1;
+            e.ghost_a = sa == 0 ? D.n[a] + 1 : 0;
+            e.ghost_b = sb == 0 ? D.n[b] + 1 : 0;
+            for (int f = 0; f < 4; ++f) e.arr[f] = D.arr[f];
+            e.pitch = D.blk.pitch; e.plane = D.plane;
+            e.flag = D.flags + 6 + 4 * pi + 2 * (1 - sa) + (1 - sb);
+            any = true;
+          }
+      if (any && !o.no_edges) W3(w3d_plan_set_edges(k.plan, edges));
+      W3(w3d_plan_enable_pairs(k.plan, k.arr[2], k.arr[3], peer_aux, o.pair_variant, o.zchunk));
+    }
     if (o.verbose && r == 0) std::printf("plan (%d x %d x %d ranks): %s\n", o.dims[0], o.dims[1], o.dims[2], w3d_plan_describe(k.plan));
   }
   if (!pair && o.kernel != "fused") {

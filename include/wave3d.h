@@ -145,15 +145,36 @@ int w3d_step_box(W3dPlan* plan, int s, double a, double b, double cscale, double
  *
  * Faces with a neighbour — w3d_plan_pair_mode() tells which protocol the plan uses:
  *   W3D_PAIR_LOCAL  no face has a neighbour: nothing to exchange.
- *   W3D_PAIR_WIDE   ghost_depth 2 and neighbours along at most one axis: ONE launch and ONE
- *       handshake per two steps.  `cur` must hold two valid ghost layers and `prev` one; the
+ *   W3D_PAIR_WIDE   ghost_depth 2 and neighbours along one axis, or along several with the edge peers
+ *       of w3d_plan_set_edges: ONE launch and ONE handshake per two steps.  `cur` must hold two valid ghost layers and `prev` one; the
  *       pass also forms level n+1 on the first ghost layer (kept in out1's ghosts for the next
  *       pass), completes level n+2 on every owned node, ships its two outermost layers per face
  *       into the neighbours' ghost layers of their `out2` and releases level s+2.
- *   W3D_PAIR_FIXUP  otherwise (one ghost layer, or neighbours along two or three axes — the
- *       wide scheme would also need the edge lines of the diagonal neighbours): nodes next to a
+ *   W3D_PAIR_FIXUP  otherwise (one ghost layer, or neighbours along two or three axes without the
+ *       edge peers): nodes next to a
  *       face with a neighbour are left out of `out2`; the pass ships level n+1 (one layer,
  *       releases s+1) and the caller finishes the layer with w3d_step_fixup. */
+/* Wide halo on 3-D blocks (neighbours along two or three axes): the two-step stencil also reaches the
+ * DIAGONAL neighbours across the block's edges, so besides the six faces up to twelve edge lines are
+ * exchanged.  Edge e = 4 * pair + 2 * sa + sb with pair 0 = (x,y), 1 = (x,z), 2 = (y,z) and sa, sb = my
+ * sides of the two axes (0 low, 1 high).  edges[e] describes the rank diagonally across that edge: its four
+ * arrays (local index origin, index order as in w3d_plan_enable_pairs), its strides, the indices
+ * (ghost_a, ghost_b) of ITS ghost line that my edge line fills, and its incoming flag word for this edge —
+ * word 6 + e' of its flags_in, e' being the same edge seen from there (sides flipped).  flags_in of this
+ * plan must then hold W3D_FLAG_WORDS words.  Call before w3d_plan_enable_pairs; an edge is needed wherever
+ * two faces on different axes both have a neighbour, and if one is missing the plan falls back to
+ * W3D_PAIR_FIXUP.  Pass NULL to clear. */
+#define W3D_EDGES 12
+#define W3D_FLAG_WORDS 18
+typedef struct W3dEdgePeer {
+  int32_t active;
+  int32_t ghost_a, ghost_b;
+  double* arr[4];
+  int64_t pitch, plane;
+  unsigned long long* flag;
+} W3dEdgePeer;
+int w3d_plan_set_edges(W3dPlan* plan, const W3dEdgePeer* edges /* [W3D_EDGES] or NULL */);
+
 #define W3D_PAIR_LOCAL 0
 #define W3D_PAIR_WIDE 1
 #define W3D_PAIR_FIXUP 2

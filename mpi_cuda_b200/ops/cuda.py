@@ -39,6 +39,16 @@ class W3dPlanDesc(C.Structure):
                 ("n_err_peers", C.c_int32), ("ghost_depth", C.c_int32), ("plane_stride", C.c_int64)]
 
 
+class W3dEdgePeer(C.Structure):
+    """The rank diagonally across one edge of the block (include/wave3d.h: w3d_plan_set_edges)."""
+    _fields_ = [("active", C.c_int32), ("ghost_a", C.c_int32), ("ghost_b", C.c_int32), ("arr", C.c_void_p * 4),
+                ("pitch", C.c_int64), ("plane", C.c_int64), ("flag", C.c_void_p)]
+
+
+EDGE_PAIRS = ((0, 1), (0, 2), (1, 2))      # edge e = 4 * pair + 2 * sa + sb
+FLAG_WORDS = 18                            # 6 faces + 12 edges
+
+
 class W3dStepper(C.Structure):
     """Which arrays hold the newest level and the one before (include/wave3d.h)."""
     _fields_ = [("level", C.c_int32), ("cur", C.c_int32), ("prev", C.c_int32), ("reserved", C.c_int32)]
@@ -78,6 +88,7 @@ def lib() -> C.CDLL:
     l.w3d_step_fused_on.argtypes = [vp, C.c_int, C.c_int, C.c_int, dbl, dbl, dbl, dbl, vp, vp]
     l.w3d_plan_pair_mode.argtypes = [vp]
     l.w3d_plan_pairs_enabled.argtypes = [vp]
+    l.w3d_plan_set_edges.argtypes = [vp, C.POINTER(W3dEdgePeer)]
     l.w3d_stepper_reset.argtypes = [C.POINTER(W3dStepper)]
     l.w3d_stepper_reset.restype = None
     l.w3d_advance_pair.argtypes = [vp, C.POINTER(W3dStepper), vp, vp, vp, vp, vp]
@@ -257,6 +268,18 @@ class CudaPlan:
     def step_box(self, s, a, b, cscale, ct, lo=None, hi=None, err_out=None, slot=0) -> None:
         check(lib().w3d_step_box(self._h, s, a, b, cscale, ct, _box(lo), _box(hi), self._err_ptr(err_out),
                                  slot, stream_ptr()))
+
+    def set_edges(self, edges: dict) -> None:
+        """edges: edge index -> dict(arr=(4 addresses), ghost=(ga, gb), pitch=, plane=, flag=address); before enable_pairs."""
+        tab = (W3dEdgePeer * 12)()
+        for e, spec in edges.items():
+            q = tab[e]
+            q.active = 1
+            q.ghost_a, q.ghost_b = spec["ghost"]
+            for i in range(4):
+                q.arr[i] = spec["arr"][i]
+            q.pitch, q.plane, q.flag = spec["pitch"], spec["plane"], spec["flag"]
+        check(lib().w3d_plan_set_edges(self._h, tab))
 
     def enable_pairs(self, aux0: torch.Tensor, aux1: torch.Tensor, pair_variant: int = -1, zchunk: int = 0,
                      peer_aux: Optional[dict] = None) -> None:

@@ -38,7 +38,7 @@ from ..utils.report import RunResult
 from .decomp import RankBlock, local_tables, plan_all, plan_rank
 from .exchange import step_coeffs
 
-_FLAG_BYTES = 256     # 6 flag words + padding, at the head of the symmetric buffer
+_FLAG_BYTES = 256     # 6 face + 12 edge flag words + padding, at the head of the symmetric buffer
 _SLOTS = 2            # error-table entries per rank and level (step kernel, fix-up pass)
 
 
@@ -66,7 +66,10 @@ class _Layout:
 class FusedSolver:
     def __init__(self, p: WaveProblem, dims: Sequence[int] = (1, 1, 1), device: Optional[torch.device] = None,
                  group=None, every: int = 2, variant: int = -1, zchunk: int = 0, use_graph: bool = True,
-                 spin_timeout_ms: int = 0, pair: bool = True, pair_variant: int = -1):
+                 spin_timeout_ms: int = 0, pair: bool = True, pair_variant: int = -1, wide_edges: bool = True):
+        """``wide_edges``: on 3-D blocks (neighbours along two or three axes) also exchange the edge lines with
+        the diagonal neighbours, so that two steps share one launch and one handshake there too; ``False``
+        keeps the fix-up protocol (a second launch per pair) for such blocks."""
         self._launches_per_run = p.K
         self.pair = bool(pair)
         # pair mode never reads array 1 before overwriting it (the first pass skips the previous
@@ -156,6 +159,25 @@ class FusedSolver:
         self.final_index = None          # array index (0..3) holding the newest level after stepping in pair mode
         self.pair_mode = cuda.PAIR_LOCAL
         if self.pair:
+            # 3-D blocks: the two-step stencil also reaches the ranks diagonally across the block's edges
+            edges = {}
+            for pi, (a, b) in enumerate(cuda.EDGE_PAIRS):
+                for sa in range(2):
+                    for sb in range(2):
+                        ra = blk.nbr[a][sa]
+                        if ra < 0 or blk.nbr[b][sb] < 0:
+                            continue
+                        r = blocks[ra].nbr[b][sb]          # neighbour of the neighbour = the diagonal rank
+                        pb, pl = blocks[r], lay[r]
+                        base = (base_ptrs[r] if self.world > 1 else base_ptrs[0])
+                        o = base + f0 + pl.origin
+                        edges[4 * pi + 2 * sa + sb] = dict(
+                            arr=tuple(o + q * fbytes for q in range(4)),
+                            ghost=(pb.n[a] + 1 if sa == 0 else 0, pb.n[b] + 1 if sb == 0 else 0),
+                            pitch=pl.pitch, plane=pl.plane,
+                            flag=base + 8 * (6 + 4 * pi + 2 * (1 - sa) + (1 - sb)))
+            if edges and wide_edges:
+                self.plan.set_edges(edges)
             self.plan.enable_pairs(self.aux[0], self.aux[1], pair_variant, zchunk, peer_aux)
             self.pair_mode = self.plan.pair_mode
 
@@ -452,7 +474,7 @@ class FusedSolver:
         self.alloc[prev].copy_(st["fields"][1])
         self.level, self._cur, self._prev, self.final_index = level, cur, prev, cur
         # ghosts of `level` are part of the dump: tell the kernels they have arrived
-        self.flags[:6].fill_(level)
+        self.flags[:cuda.FLAG_WORDS].fill_(level)
         self.barrier()
         return level
 

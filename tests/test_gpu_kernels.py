@@ -223,7 +223,7 @@ def test_watchdog_trips_instead_of_hanging(pair):
     # (pair: two periodic axes = the fix-up protocol, whose pair pass waits for a flag that only a
     # previous fix-up launch releases; a wide-halo plan on ONE GPU publishes to itself at kernel entry)
     p = WaveProblem(48, 2.0, 1e-3, 4, bc="dpp" if pair else "ddp")
-    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, spin_timeout_ms=30, pair=pair)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, spin_timeout_ms=30, pair=pair, wide_edges=False)
     s.init()
     if pair:
         s.pair_advance(2)         # level 2 was never produced: its flag cannot arrive
@@ -236,23 +236,25 @@ def test_watchdog_trips_instead_of_hanging(pair):
     s.check_status()
 
 
-@pytest.mark.parametrize("pair,at,bc", [(False, 6, "dpd"), (True, 6, "dpd"), (True, 5, "dpd"), (True, 4, "ppd")])
-def test_checkpoint_restart_is_bit_exact(tmp_path, pair, at, bc):
+@pytest.mark.parametrize("pair,at,bc,edges", [(False, 6, "dpd", True), (True, 6, "dpd", True), (True, 5, "dpd", True),
+                                              (True, 4, "ppd", False), (True, 5, "ppd", True)])
+def test_checkpoint_restart_is_bit_exact(tmp_path, pair, at, bc, edges):
     """Dump after level `at`, restore into a fresh solver, finish: same field and trace as one run.
 
     Pair mode: the live levels sit in any two of the four arrays (the dump records which), an odd
-    `at` leaves the newest level produced by a single step, and "ppd" runs the fix-up protocol."""
+    `at` leaves the newest level produced by a single step, and "ppd" runs the fix-up protocol
+    (edges=False) or the wide halo with edge lines (edges=True)."""
     from mpi_cuda_b200.parallel.fused import FusedSolver
     p = WaveProblem((60, 44, 36), 2.0, 1e-3, 10, bc=bc)
-    a = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=pair)
+    a = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=pair, wide_edges=edges)
     full = a.run().trace
     want = a.final_field().clone()
-    b = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=pair)
+    b = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=pair, wide_edges=edges)
     b.init()
     b.run_range(1, at)
     ck = b.save_checkpoint(str(tmp_path / "ck"), at)
     assert ck.endswith(".rank0.pt")
-    c = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=pair)
+    c = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=pair, wide_edges=edges)
     level = c.load_checkpoint(str(tmp_path / "ck"))
     assert level == at
     c.run_range(level + 1, p.K)
@@ -332,9 +334,11 @@ def test_native_mpigpu_executable_matches_python_path():
     per2 = subprocess.run([exe, "96", "0.001", "9", "--bc", "pdp", "--L", "2", "--every", "1"], capture_output=True, text=True, check=True).stdout
     base2, _ = cpu.solve(WaveProblem(96, 2.0, 1e-3, 9, bc="pdp"), every=1)
     got2 = [report.parse_step(l) for l in per2.splitlines() if l.startswith("Step ")]
-    assert "fix-up" in per2 and len(got2) == 9
+    assert "wide halo" in per2 and len(got2) == 9      # edge lines to the diagonal neighbour (the GPU itself)
     for g, b in zip(got2, base2):
         assert abs(g[2] - b[2]) <= 1e-6 * b[2] and abs(g[3] - b[3]) <= 1e-6 * b[3]
+    per3 = subprocess.run([exe, "96", "0.001", "9", "--bc", "pdp", "--L", "2", "--every", "1", "--fixup"], capture_output=True, text=True, check=True).stdout
+    assert "fix-up" in per3 and [l for l in per3.splitlines() if l.startswith("Step ")] == [l for l in per2.splitlines() if l.startswith("Step ")]
 
 
 @pytest.mark.parametrize("pair_variant", [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10])
@@ -354,18 +358,19 @@ def test_pair_kernel_bit_exact_vs_cpu(N, K, pair_variant):
         assert a[2] == c[2] and abs(a[3] - c[3]) <= 1e-12 * c[3]
 
 
-@pytest.mark.parametrize("bc", ["ddp", "dpd", "pdd", "ppp", "dpp"])
+@pytest.mark.parametrize("bc,edges", [("ddp", True), ("dpd", True), ("pdd", True), ("ppp", True), ("dpp", True), ("pdp", True),
+                                      ("ppd", True), ("ppp", False), ("dpp", False)])
 @pytest.mark.parametrize("K", [6, 7])
-def test_pair_mode_with_periodic_faces_matches_cpu(bc, K):
+def test_pair_mode_with_periodic_faces_matches_cpu(bc, edges, K):
     """Two-step passes with in-kernel halo exchange (periodic axes wrap onto the GPU itself).
 
-    One periodic axis: wide halo (one launch, one handshake per two steps); two or three:
-    the fix-up protocol."""
+    One periodic axis: wide halo (one launch, one handshake per two steps).  Two or three: wide halo with the
+    edge lines of the diagonal neighbours (here the GPU itself), or — edges=False — the fix-up protocol."""
     from mpi_cuda_b200.ops import cuda
     from mpi_cuda_b200.parallel.fused import FusedSolver
     p = WaveProblem((70, 45, 37), 2.0, 1e-3, K, bc=bc)
-    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=True)
-    assert s.pair_mode == (cuda.PAIR_WIDE if bc.count("p") == 1 else cuda.PAIR_FIXUP)
+    s = FusedSolver(p, (1, 1, 1), _dev(), every=1, use_graph=False, pair=True, wide_edges=edges)
+    assert s.pair_mode == (cuda.PAIR_WIDE if (bc.count("p") == 1 or edges) else cuda.PAIR_FIXUP)
     res = s.run()
     s.check_status()
     ref, _, _ = _cpu_fields(p, K)

@@ -31,12 +31,15 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 L_BOX = 2.0
 
 
-def case(mode, dims, bc, N, K, graph=False, delay=False, zchunk=0):
-    return dict(mode=mode, dims=tuple(dims), bc=bc, N=tuple(N), K=K, graph=graph, delay=delay, zchunk=zchunk)
+def case(mode, dims, bc, N, K, graph=False, delay=False, zchunk=0, edges=True):
+    """edges=False: blocks with neighbours along two or three axes use the fix-up protocol instead of the
+    wide halo with edge lines."""
+    return dict(mode=mode, dims=tuple(dims), bc=bc, N=tuple(N), K=K, graph=graph, delay=delay, zchunk=zchunk,
+                edges=edges)
 
 
 def _key(c):
-    return (c["mode"], c["dims"], c["bc"], c["N"], c["K"], c["graph"], c["delay"], c["zchunk"])
+    return (c["mode"], c["dims"], c["bc"], c["N"], c["K"], c["graph"], c["delay"], c["zchunk"], c["edges"])
 
 
 SMALL = (72, 60, 52)
@@ -48,26 +51,36 @@ CASES = {
        # delayed ranks
        + [case("fused", (1, 1, 2), "ddp", SMALL, 12, delay=True),
           case("pair", (1, 1, 2), "ddp", SMALL, 12, delay=True),        # wide halo
-          case("pair", (1, 2, 1), "ddp", SMALL, 12, delay=True),        # fix-up protocol (two axes)
+          case("pair", (1, 2, 1), "ddp", SMALL, 12, delay=True),        # two axes: wide halo with edge lines
+          case("pair", (1, 2, 1), "ddp", SMALL, 12, delay=True, edges=False),   # two axes: fix-up protocol
+          case("pair", (2, 1, 1), "dpp", SMALL, 8, delay=True),         # three axes, x split: edges to the other GPU and to itself
           case("pair", (2, 1, 1), "ddd", SMALL, 9, delay=True)]         # wide halo across x
        # tiles that end one layer short of the face, delayed ranks
        + [case("pair", (1, 2, 1), "ddd", (40, 67, 30), 8, delay=True),      # n_y = 33 + 33
-          case("pair", (1, 2, 1), "ddp", (40, 67, 30), 8, delay=True),      # same, fix-up protocol
+          case("pair", (1, 2, 1), "ddp", (40, 67, 30), 8, delay=True),      # same with a second axis (edge lines)
+          case("pair", (1, 2, 1), "ddp", (40, 67, 30), 8, delay=True, edges=False),   # same, fix-up protocol
           case("pair", (1, 2, 1), "ddd", (64, 514, 24), 6, delay=True),     # 513 -> 257 + 256
           case("pair", (2, 1, 1), "ddd", (131, 30, 30), 8, delay=True),     # n_x = 65 + 65
-          case("pair", (2, 1, 1), "dpd", (131, 30, 30), 8, delay=True),     # same, fix-up protocol
+          case("pair", (2, 1, 1), "dpd", (131, 30, 30), 8, delay=True),     # same with a second axis (edge lines)
+          case("pair", (2, 1, 1), "dpd", (131, 30, 30), 8, delay=True, edges=False),  # same, fix-up protocol
           case("pair", (1, 1, 2), "ddd", (40, 40, 131), 8, delay=True, zchunk=64),   # last chunk = 1 plane
-          case("pair", (1, 1, 2), "pdd", (40, 40, 131), 8, delay=True, zchunk=64)],  # same, fix-up protocol
+          case("pair", (1, 1, 2), "pdd", (40, 40, 131), 8, delay=True, zchunk=64),   # same with a second axis (edge lines)
+          case("pair", (1, 1, 2), "pdd", (40, 40, 131), 8, delay=True, zchunk=64, edges=False)],  # same, fix-up protocol
     4: [case("pair", d, "dpd", (80, 72, 64), 8) for d in [(1, 2, 2), (2, 2, 1), (1, 1, 4), (1, 4, 1)]]
        + [case("fused", d, "dpd", (80, 72, 64), 8) for d in [(1, 2, 2), (2, 2, 1)]]
        + [case("pair", (1, 1, 4), "ddd", (80, 72, 64), 9, delay=True),
           case("pair", (1, 1, 4), "ddp", (80, 72, 64), 8, delay=True),
-          case("pair", (1, 2, 2), "ddd", (80, 72, 64), 8, delay=True)],
+          case("pair", (1, 2, 2), "ddd", (80, 72, 64), 8, delay=True),
+          case("pair", (1, 2, 2), "ddd", (80, 72, 64), 8, delay=True, edges=False),
+          case("pair", (2, 2, 1), "ddp", (80, 72, 64), 9, delay=True),
+          case("pair", (1, 2, 2), "ppp", (80, 72, 64), 8, graph=True)],
     8: [case("pair", (1, 1, 8), "ddd", (96, 80, 128), 10, delay=True),
         case("pair", (1, 1, 8), "ddp", (96, 80, 128), 10, graph=True),
         case("pair", (2, 2, 2), "ddd", (96, 80, 64), 8, delay=True),
         case("pair", (1, 2, 4), "ddd", (96, 80, 64), 8),
         case("pair", (1, 2, 4), "pdp", (96, 80, 64), 8, delay=True),
+        case("pair", (2, 2, 2), "ddd", (96, 80, 64), 8, delay=True, edges=False),
+        case("pair", (2, 2, 2), "ppp", (96, 80, 64), 9, graph=True),
         case("fused", (1, 1, 8), "ddd", (96, 80, 128), 10),
         case("fused", (2, 2, 2), "ppp", (96, 80, 64), 8),
         case("nccl", (1, 2, 4), "ddd", (96, 80, 64), 8)],
@@ -86,7 +99,7 @@ def _run_case(rank, world, c):
         return s.run().trace, "nccl"
     pair = c["mode"] == "pair"
     s = FusedSolver(p, c["dims"], dev, every=2, use_graph=c["graph"], spin_timeout_ms=20000, pair=pair,
-                    zchunk=c["zchunk"])
+                    zchunk=c["zchunk"], wide_edges=c["edges"])
     if not c["delay"]:
         r = s.run()
         r2 = s.run()
@@ -148,13 +161,13 @@ def _check(world, c):
             from mpi_cuda_b200.ops import cuda
             p = WaveProblem(c["N"], L_BOX, 1e-3, c["K"], bc=c["bc"])
             axes = sum(1 for d in range(3) if c["dims"][d] > 1 or p.periodic[d])
-            assert mode == (cuda.PAIR_WIDE if axes == 1 else cuda.PAIR_FIXUP)
+            assert mode == (cuda.PAIR_WIDE if (axes == 1 or c["edges"]) else cuda.PAIR_FIXUP)
 
 
 def _id(c):
     return "-".join([c["mode"], "x".join(map(str, c["dims"])), c["bc"], "x".join(map(str, c["N"])), f"K{c['K']}"]
                     + (["graph"] if c["graph"] else []) + (["delay"] if c["delay"] else [])
-                    + ([f"zc{c['zchunk']}"] if c["zchunk"] else []))
+                    + ([f"zc{c['zchunk']}"] if c["zchunk"] else []) + ([] if c["edges"] else ["fixup"]))
 
 
 @pytest.mark.parametrize("c", CASES[2], ids=_id)
