@@ -181,6 +181,8 @@ def main() -> int:
                     help="temporal blocking: two time steps per pass over memory (default)")
     ap.add_argument("--no-pair", dest="pair", action="store_false", help="one pass per time step")
     ap.add_argument("--pair-variant", type=int, default=-1)
+    ap.add_argument("--fixup", action="store_true",
+                    help="3-D blocks: fix-up protocol (second launch per pair) instead of the wide halo with edge lines")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm()
@@ -224,7 +226,8 @@ def main() -> int:
     if args.backend == "fused":
         from mpi_cuda_b200.parallel.fused import FusedSolver, StreamingSession
         s = FusedSolver(p, dims, device, every=args.every, variant=args.variant, zchunk=args.zchunk,
-                        use_graph=not args.no_graph, pair=args.pair, pair_variant=args.pair_variant)
+                        use_graph=not args.no_graph, pair=args.pair, pair_variant=args.pair_variant,
+                        wide_edges=not args.fixup)
         # ---- warm-up: W untimed steps (also loads the module, maps peers) ----
         s.init()
         s._enqueue_steps(1, min(W, K))

@@ -99,3 +99,42 @@ def test_auto_decomposition_policy():
     assert decomp.parse_dims("auto", 8, (63, 63, 63)) == (1, 2, 4)         # slabs would be thinner than 8 planes
     assert decomp.parse_dims("auto", 1, (511, 511, 511)) == (1, 1, 1)
     assert decomp.parse_dims("auto", 4) == (1, 2, 2)
+
+
+def test_local_tables_with_two_ghost_layers():
+    """Tables for the wide-halo layout: n + 4 entries, wrapped on periodic axes, 0 beyond a Dirichlet boundary."""
+    import numpy as np
+    from mpi_cuda_b200.models.analytic import axis_table
+    p = WaveProblem(32, 1.0, 1e-3, 1, bc="ddp")
+    dims = (1, 1, 4)
+    for r in range(4):
+        b = decomp.plan_rank(p, dims, r)
+        one = decomp.local_tables(p, b, ghosts=1)
+        two = decomp.local_tables(p, b, ghosts=2)
+        for d in range(3):
+            assert len(two[d]) == b.n[d] + 4
+            assert np.array_equal(two[d][1:-1], one[d])          # the inner n + 2 entries are the classic table
+        full_z = axis_table(p, 2)
+        g = np.arange(b.lo[2] - 2, b.lo[2] + b.n[2] + 2) % p.N[2]
+        assert np.array_equal(two[2], full_z[g])                 # periodic axis: wrapped
+        assert two[0][0] == 0.0 and two[0][-1] == 0.0            # Dirichlet axis: nothing beyond the boundary node
+        assert two[0][1] == 0.0 and two[0][-2] == 0.0            # (the boundary node itself)
+
+
+def test_diagonal_neighbours_are_neighbours_of_neighbours():
+    """The wide halo on 3-D blocks sends edge lines to the rank diagonally across an edge; FusedSolver and
+    mpigpu find it as the neighbour of the neighbour.  Check that this is symmetric and order-independent."""
+    for bc, dims in (("ddd", (2, 2, 2)), ("ppp", (1, 2, 4)), ("dpd", (2, 2, 1)), ("ppp", (1, 1, 1))):
+        p = WaveProblem(24, 1.0, 1e-3, 1, bc=bc)
+        blocks = decomp.plan_all(p, dims)
+        for b in blocks:
+            for a, c in ((0, 1), (0, 2), (1, 2)):
+                for sa in range(2):
+                    for sc in range(2):
+                        if b.nbr[a][sa] < 0 or b.nbr[c][sc] < 0:
+                            continue
+                        d1 = blocks[b.nbr[a][sa]].nbr[c][sc]
+                        d2 = blocks[b.nbr[c][sc]].nbr[a][sa]
+                        assert d1 == d2 >= 0                                   # either way round
+                        back = blocks[blocks[d1].nbr[a][1 - sa]].nbr[c][1 - sc]
+                        assert back == b.rank                                  # and the diagonal's diagonal is me

@@ -158,3 +158,32 @@ def test_roofline_arithmetic():
     slab = roofline.step_roofline(plan_all(p, (1, 1, 8)), True, 6539.9)
     assert slab["halo_bytes_per_gpu_per_step"] == 2 * 511 * 511 * 8
     assert slab["roofline_ms_per_step"] < one["roofline_ms_per_step"] / 8 * 1.1
+
+
+def test_bench_validates_every_line_against_the_published_trace():
+    """bench.py's own guard: the headline config is checked line by line against report.pdf p.15-16."""
+    import importlib.util
+    import os
+    from mpi_cuda_b200 import WaveProblem
+    from mpi_cuda_b200.utils import report
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    p = WaveProblem(512, 1.0, 1e-3, 20)
+    good = [tuple(g) for g in report.GOLDEN_512]
+    ok, how = bench.validate_trace(p, good, 2)
+    assert ok and "published" in how
+    bad = list(good)
+    n, t, mx, l2 = bad[4]
+    bad[4] = (n, t, mx + 2e-14, l2)                   # a stale ghost moves Max by more than round-off
+    assert bench.validate_trace(p, bad, 2)[0] is False
+    assert bench.validate_trace(p, good[:-1], 2)[0] is False        # a missing line is a failure too
+    # any other configuration: closed-form oracle on every line
+    from mpi_cuda_b200.models.analytic import oracle_trace
+    q = WaveProblem(64, 2.0, 1e-3, 10, bc="ddp")
+    tr = oracle_trace(q, 2)
+    ok, how = bench.validate_trace(q, tr, 2)
+    assert ok and "oracle" in how
+    tr[2] = (tr[2][0], tr[2][1], tr[2][2] * 1.001, tr[2][3])
+    assert bench.validate_trace(q, tr, 2)[0] is False
