@@ -201,12 +201,20 @@ int main(int argc, char** argv) {
       CK(cudaMemcpy(k.tab_alloc[d], t.data(), t.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
   }
-  // ---- peer access between all GPUs of the run ----
+  // ---- peer access: face neighbours and, for 3-D blocks, the diagonal neighbours across the edges ----
   for (int r = 0; r < G; ++r)
     for (int q = 0; q < G; ++q) {
       if (q == r) continue;
       bool needed = false;
-      for (int d = 0; d < 3; ++d) needed = needed || R[r].nbr[d][0] == q || R[r].nbr[d][1] == q;
+      for (int d = 0; d < 3; ++d)
+        for (int s = 0; s < 2; ++s) {
+          const int f = R[r].nbr[d][s];
+          if (f < 0) continue;
+          needed = needed || f == q;
+          for (int d2 = 0; d2 < 3; ++d2)
+            for (int s2 = 0; s2 < 2; ++s2)
+              if (d2 != d && R[f].nbr[d2][s2] == q && R[r].nbr[d2][s2] >= 0) needed = true;   // neighbour of the neighbour
+        }
       if (!needed) continue;
       CK(cudaSetDevice(r));
       int can = 0;
