@@ -31,9 +31,11 @@
 //     out1's ghost layer as the next pass's u^{n-1} halo; level 2 is then complete on
 //     every owned node and the face CTAs ship its two outermost layers per face.  Same
 //     halo volume per step as one layer per step.
-//   * fix-up (two axes with neighbours: the wide scheme would also need the edge lines of
-//     the diagonal neighbours): one ghost layer; level 2 is left out next to such faces
-//     (skip_lo/hi) and finished by `fixup_kernel` after an exchange of level 1.
+//     On 3-D blocks the two-step stencil also reaches the diagonal neighbours across the
+//     block's edges; with their edge lines (w3d_plan_set_edges, edge_copy_out) blocks run
+//     the same protocol.
+//   * fix-up (one ghost layer, or blocks without edge peers): level 2 is left out next to faces
+//     with a neighbour (skip_lo/hi) and finished by `fixup_kernel` after an exchange of level 1.
 // The arithmetic is the same w3d_partial/w3d_finish sequence, so results are
 // bit-identical to two single steps.
 #pragma once

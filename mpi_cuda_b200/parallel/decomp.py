@@ -53,11 +53,12 @@ def default_dims(world: int, kind: str = "block") -> Tuple[int, int, int]:
 def auto_dims(world: int, unknowns: Sequence[int]) -> Tuple[int, int, int]:
     """Measured policy (profiles/scaling.md): z slabs whenever every rank keeps at least 8 planes.
 
-    With neighbours along one axis only, two time steps share one launch and one halo handshake
-    (wide-halo protocol); with two or three axes the fix-up protocol needs a second
-    launch per pair.  On the per-GPU blocks of 1024^3 and 2048^3 over 8 GPUs the slab is 7 % faster
-    than the 1x2x4 block (0.400 vs 0.432 and 3.08 vs 3.31 ms per step) although it ships more halo:
-    NVLink 5 is nowhere near a limit here.  3-D blocks remain for very thin slabs and on request."""
+    Every decomposition runs the wide-halo protocol (one launch and one halo handshake per two time
+    steps), so what decides is the cost of the faces: z faces leave from registers inside
+    the streaming loop, x / y faces are strided copy-outs after it.  On 8 GPUs slabs win at 512^3
+    (0.0552 vs 0.0599 ms per step for 1x2x4) and are within 2 % of 1x2x4 blocks at 1024^3 (0.418 vs
+    0.409): NVLink 5 is nowhere near a limit, halo volume does not matter.  3-D blocks remain for very
+    thin slabs and on request."""
     if world > 1 and unknowns[2] // world >= 8:
         return default_dims(world, "slab")
     return default_dims(world, "block")

@@ -251,8 +251,9 @@ class FusedSolver:
 
         Array roles rotate over the four arrays: (cur, prev) -> (out1, out2) = (0,1)->(2,3),
         (3,2)->(0,1), (1,0)->(2,3), ...  With neighbours (or periodic axes) the pass also does the
-        halo exchange: wide-halo protocol = this one launch; fix-up protocol (neighbours along
-        two or three axes) = a second launch that finishes level n+2 next to those faces."""
+        halo exchange: wide-halo protocol = this one launch (3-D blocks: edge lines to the diagonal neighbours
+        included); fix-up protocol (``wide_edges=False`` on 3-D blocks) = a second launch that finishes level
+        n+2 next to those faces."""
         cur, prev = self._cur, self._prev
         out1, out2 = (2, 3) if cur in (0, 1) else (0, 1)
         l1 = step_coeffs(n + 1) + (float(self.ct[n + 1]),)

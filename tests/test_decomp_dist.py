@@ -93,7 +93,7 @@ def test_gloo_rank_count_invariance(world, dims, bc):
 
 def test_auto_decomposition_policy():
     assert decomp.parse_dims("auto", 8, (511, 511, 511)) == (1, 1, 8)      # 63 planes per rank: slab
-    assert decomp.parse_dims("auto", 8, (1023, 1023, 1023)) == (1, 1, 8)   # one axis with neighbours: one launch per pair
+    assert decomp.parse_dims("auto", 8, (1023, 1023, 1023)) == (1, 1, 8)   # z faces are the cheap ones
     assert decomp.parse_dims("auto", 8, (2047, 2047, 2047)) == (1, 1, 8)
     assert decomp.parse_dims("auto", 8, (255, 255, 255)) == (1, 1, 8)
     assert decomp.parse_dims("auto", 8, (63, 63, 63)) == (1, 2, 4)         # slabs would be thinner than 8 planes
