@@ -236,7 +236,10 @@ class CudaPlan:
     def __del__(self):
         h = getattr(self, "_h", None)
         if h:
-            lib().w3d_plan_destroy(h)
+            try:
+                lib().w3d_plan_destroy(h)
+            except Exception:          # interpreter shutdown: the module globals may already be gone
+                pass
             self._h = None
 
     def describe(self) -> str:
@@ -365,11 +368,15 @@ class NativeSession:
         self._step, self._result = lib().w3d_session_step_async, lib().w3d_session_result
 
     def close(self) -> None:
-        if self._h:
+        if getattr(self, "_h", None):
             lib().w3d_session_destroy(self._h)
             self._h = None
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:              # interpreter shutdown
+            pass
 
     def begin(self, level: int = 0, cur: int = 0, prev: int = 1) -> None:
         st = W3dStepper(level, cur, prev, 0)
